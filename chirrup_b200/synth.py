@@ -1,0 +1,137 @@
+"""Seeded synthetic RWKV-7 ("x070") checkpoints with the exact key set / shapes Albatross expects.
+
+There is no network for real ``.pth`` files, so parity tests and ``bench.py`` run on random-init weights of the
+named geometry.  Keys and raw (pre-transform) shapes follow what ``RWKV_x070.__init__`` /
+``get_gpu_parameter_groups`` index (``/root/reference/Albatross/rwkv7.py:171-221``, ``:394-492``): note that
+``blocks.0.att.v0/v1/v2`` must exist even though layer 0 ignores them (``:438-443``, ``:636``).
+
+Two recipes:
+
+* ``plain``  — independent Gaussians scaled so activations stay O(1) through the stack (logit std ~ 1).
+* ``margin`` — same, but ``head.weight`` gets an extra component aligned with a permutation of the ln0-normalised
+  embedding, so the greedy argmax has a margin far above fp16 noise while every layer still contributes to the
+  logits.  Used for the "token-identical greedy for 256 steps" check (SURVEY.md §7 "hard parts").
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, Optional
+
+import torch
+
+HEAD_SIZE = 64
+
+
+@dataclass(frozen=True)
+class Geometry:
+    name: str
+    n_layer: int
+    n_embd: int
+    d_w: int
+    d_a: int
+    d_v: int
+    d_g: int
+    vocab_size: int = 65536
+
+    @property
+    def n_head(self) -> int:
+        return self.n_embd // HEAD_SIZE
+
+    @property
+    def d_ffn(self) -> int:
+        return 4 * self.n_embd
+
+    def wkv_bytes_per_token(self) -> int:
+        """Algorithmic bytes of the WKV + state step per (request, token): SURVEY.md §8(d)."""
+        H, C = self.n_head, self.n_embd
+        return self.n_layer * (2 * H * 64 * 64 * 2 + 7 * C * 2 + 4)
+
+    def gemm_flops_per_token(self) -> int:
+        C, L, V = self.n_embd, self.n_layer, self.vocab_size
+        lora = self.d_w + self.d_a + self.d_v + self.d_g
+        return L * 2 * (12 * C * C + 2 * C * lora) - 2 * 2 * C * self.d_v + 2 * C * V
+
+
+GEOMETRIES = {
+    # tiny geometries for CPU-speed tests (not BASELINE configs)
+    "tiny": Geometry("tiny", 2, 128, 32, 32, 32, 32, vocab_size=512),
+    "small": Geometry("small", 3, 256, 64, 64, 32, 64, vocab_size=1024),
+    # BASELINE.json configs
+    "0.1B": Geometry("0.1B", 12, 768, 64, 64, 32, 128),
+    "1.5B": Geometry("1.5B", 24, 2048, 96, 96, 64, 256),
+    "7.2B": Geometry("7.2B", 32, 4096, 128, 128, 96, 480),
+    "13.3B": Geometry("13.3B", 61, 4096, 128, 128, 96, 480),
+}
+
+
+def make_checkpoint(geom: Geometry, seed: int = 0, recipe: str = "plain", device="cpu",
+                    dtype=torch.float32, margin: float = 4.0, n_layer: Optional[int] = None) -> Dict[str, torch.Tensor]:
+    """Raw checkpoint dict (what ``torch.load(MODEL_NAME + '.pth')`` returns in the reference)."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    C, H, F_, V = geom.n_embd, geom.n_head, geom.d_ffn, geom.vocab_size
+    L = geom.n_layer if n_layer is None else n_layer
+
+    def randn(*shape, std=1.0, mean=0.0):
+        t = torch.randn(*shape, generator=g, device=device, dtype=torch.float32)
+        if std != 1.0:
+            t.mul_(std)
+        if mean != 0.0:
+            t.add_(mean)
+        return t.to(dtype)
+
+    def rand(*shape, lo=0.0, hi=1.0):
+        return (torch.rand(*shape, generator=g, device=device, dtype=torch.float32) * (hi - lo) + lo).to(dtype)
+
+    z: Dict[str, torch.Tensor] = {}
+    z["emb.weight"] = randn(V, C, std=0.5)
+    z["blocks.0.ln0.weight"] = randn(C, std=0.05, mean=1.0)
+    z["blocks.0.ln0.bias"] = randn(C, std=0.02)
+    for i in range(L):
+        b = f"blocks.{i}."
+        for ln in ("ln1", "ln2"):
+            z[b + ln + ".weight"] = randn(C, std=0.05, mean=1.0)
+            z[b + ln + ".bias"] = randn(C, std=0.02)
+        a = b + "att."
+        for n in ("x_r", "x_w", "x_k", "x_v", "x_a", "x_g"):
+            z[a + n] = rand(1, 1, C, lo=0.0, hi=1.0)
+        z[a + "w0"] = randn(1, 1, C, std=1.0, mean=-1.0)
+        z[a + "a0"] = randn(1, 1, C, std=0.5)
+        z[a + "v0"] = randn(1, 1, C, std=0.5, mean=0.5)
+        for n, d in (("w", geom.d_w), ("a", geom.d_a), ("v", geom.d_v), ("g", geom.d_g)):
+            z[a + n + "1"] = randn(C, d, std=C ** -0.5)
+            z[a + n + "2"] = randn(d, C, std=(0.5 if n != "g" else 1.0) * d ** -0.5 * (2.0 if n == "g" else 1.0))
+        z[a + "k_k"] = randn(1, 1, C, std=0.1, mean=0.85)
+        z[a + "k_a"] = randn(1, 1, C, std=0.1, mean=1.0)
+        z[a + "r_k"] = randn(H, HEAD_SIZE, std=0.1)
+        z[a + "receptance.weight"] = randn(C, C, std=C ** -0.5)
+        z[a + "key.weight"] = randn(C, C, std=C ** -0.5)
+        z[a + "value.weight"] = randn(C, C, std=C ** -0.5)
+        z[a + "output.weight"] = randn(C, C, std=0.5 * C ** -0.5)
+        z[a + "ln_x.weight"] = randn(C, std=0.05, mean=1.0)
+        z[a + "ln_x.bias"] = randn(C, std=0.02)
+        f = b + "ffn."
+        z[f + "x_k"] = rand(1, 1, C)
+        z[f + "key.weight"] = randn(F_, C, std=C ** -0.5)
+        z[f + "value.weight"] = randn(C, F_, std=0.5 * F_ ** -0.5)
+    z["ln_out.weight"] = randn(C, std=0.05, mean=1.0)
+    z["ln_out.bias"] = randn(C, std=0.02)
+    z["head.weight"] = randn(V, C, std=C ** -0.5)
+    if recipe == "margin":
+        # next-token = perm[token] by a wide margin: head row perm[t] is aligned with LN0(emb[t]).
+        emb = z["emb.weight"].float()
+        e = torch.nn.functional.layer_norm(emb, (C,), weight=z["blocks.0.ln0.weight"].float(),
+                                           bias=z["blocks.0.ln0.bias"].float())
+        perm = torch.randperm(V, generator=g, device=device)
+        head = z["head.weight"].float()
+        head[perm] += (margin / C) * e
+        z["head.weight"] = head.to(dtype)
+    elif recipe != "plain":
+        raise ValueError(recipe)
+    return z
+
+
+def save_checkpoint(path_without_ext: str, geom: Geometry, **kw) -> str:
+    z = make_checkpoint(geom, **kw)
+    torch.save(z, path_without_ext + ".pth")
+    return path_without_ext + ".pth"
