@@ -1,0 +1,64 @@
+"""ctypes binding of ``libchirrup_b200.so`` (the C ABI declared in ``include/chirrup_b200.h``).
+
+The library is the product: if it is missing it is built (nvcc) or the import fails loudly — there is no fallback path.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import re
+from typing import Dict, List
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libchirrup_b200.so")
+HEADER = os.path.join(os.path.dirname(HERE), "include", "chirrup_b200.h")
+
+_lib = None
+
+_c = ctypes
+_P = _c.c_void_p
+_I = _c.c_int
+_L = _c.c_long
+
+# name -> (restype, argtypes); must match include/chirrup_b200.h (tests/test_abi.py checks the symbol list against the header)
+SIGNATURES: Dict[str, tuple] = {
+    "b200_abi_version": (_I, []),
+    "b200_wkv7_forward_seq": (_I, [_I, _I, _I, _I, _P, _L, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "b200_wkv7_forward_one": (_I, [_I, _I, _I, _P, _L, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "b200_spmv_forward": (_I, [_I, _I, _P, _P, _P, _P]),
+    "b200_linear_f16": (_I, [_I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P, _I, _P, _L, _P]),
+    "b200_linear_workspace_bytes": (_L, [_I, _I]),
+}
+
+
+def header_symbols() -> List[str]:
+    """Function names declared in include/chirrup_b200.h."""
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", src)))
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH) or not os.environ.get("CHIRRUP_B200_NO_BUILD"):
+            from . import build as _build
+
+            _build.build()  # no-op when the in-tree library is newer than its sources
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the library does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        kind = "cudaError" if rc > 0 else "b200 error"
+        raise B200Error(f"{what} failed: {kind} {rc}")

@@ -1,0 +1,198 @@
+// WKV-7 state-forward kernels for sm_100a.
+//
+// Replaces the reference's kernel_forward_w0_fp16_dither_seq / _one
+// (/root/reference/Albatross/cuda/rwkv7_state_fwd_fp16.cu:26-97, :99-167, launchers :313-322) behind the same
+// argument meaning.  The arithmetic is the reference's, op for op (fp16 half2 chains, even/odd lane split, one rounding per
+// op, the elapsed_t dither of .cu:20-23) so the result is bit-identical to the reference kernel; what is new is the data
+// movement: the 64x64 fp16 state tile is staged global -> shared by one TMA tensor copy with the hardware 128-byte swizzle
+// (conflict-free 128-bit row reads, no software transpose), updated in registers, written back through the same swizzled
+// buffer with one TMA store.  A slot-index vector lets the caller address state rows indirectly (no physical slot swaps).
+#include "common.cuh"
+#include "tmap.h"
+#include "../../include/chirrup_b200.h"
+
+namespace b200 {
+namespace {
+
+constexpr int HS = 64;  // head size (reference: _N_ = 64, Albatross/rwkv7.py:48)
+
+// reference .cu:20-23, :59 — as compiled with --use_fast_math: FMUL, MUFU.EX2, FADD, MUFU.RCP, FMUL, MUFU.EX2, FADD, FFMA, F2F
+DEVI __half decay_dither(__half w_pre, int t) {
+    const float nlog2_e = -1.4426950408889634f;
+    const float nexp_half_log2_e = -0.8750387749145276f;
+    const float two_to_neg_41 = 4.547473508864641e-13f;
+    float x = __fmul_rn(__half2float(w_pre), nlog2_e);
+    float d = __fadd_rn(ex2_approx_ftz(x), 1.0f);
+    float q = __fmul_rn(rcp_approx_ftz(d), nexp_half_log2_e);
+    float e = __fadd_rn(ex2_approx_ftz(q), -1.0f);
+    int rot = static_cast<int>(2654435769u * static_cast<uint32_t>(t));
+    return __float2half_rn(__fmaf_rn(static_cast<float>(rot), two_to_neg_41, e));
+}
+
+struct TokenRegs {
+    __half r, w, k, v, a, b;
+};
+
+// One CTA = one (sequence, head) tile, 64 threads = one thread per value row i (holds S[i][0..63] as 32 half2).
+__global__ void __launch_bounds__(HS) wkv7_seq_kernel(const __grid_constant__ CUtensorMap tm_state, int T, int C, int H,
+                                                      int rows_per_slot, const __half* __restrict__ r_,
+                                                      const __half* __restrict__ w_, const __half* __restrict__ k_,
+                                                      const __half* __restrict__ v_, const __half* __restrict__ a_,
+                                                      const __half* __restrict__ b_, __half* __restrict__ y_,
+                                                      const int* __restrict__ elapsed_t, const int* __restrict__ slot_idx) {
+    __shared__ __align__(1024) uint8_t tile[HS * HS * 2];
+    __shared__ __align__(16) __half sv[5][HS];  // w~, k, a, b, r of the current token
+    __shared__ __align__(8) uint64_t bar;
+
+    const int bb = blockIdx.x / H;
+    const int h = blockIdx.x - bb * H;
+    const int i = threadIdx.x;
+    const int slot = slot_idx ? slot_idx[bb] : bb;
+    const int row0 = slot * rows_per_slot + h * HS;
+
+    if (i == 0) {
+        mbar_init(&bar, 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    if (i == 0) {
+        mbar_arrive_expect_tx(&bar, HS * HS * 2);
+        tma_load_2d(tile, &tm_state, 0, row0, &bar);
+    }
+
+    const int t0 = elapsed_t[bb];
+    size_t idx = (size_t)bb * T * C + (size_t)h * HS + i;
+    TokenRegs cur;
+    cur.r = r_[idx]; cur.w = w_[idx]; cur.k = k_[idx]; cur.v = v_[idx]; cur.a = a_[idx]; cur.b = b_[idx];
+
+    mbar_wait(&bar, 0);
+    __half2 S[HS / 2];
+    {
+        const int4* rowp = reinterpret_cast<const int4*>(tile + i * 128);
+        const int sw = i & 7;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            int4 q = rowp[c ^ sw];
+            S[4 * c + 0] = *reinterpret_cast<__half2*>(&q.x);
+            S[4 * c + 1] = *reinterpret_cast<__half2*>(&q.y);
+            S[4 * c + 2] = *reinterpret_cast<__half2*>(&q.z);
+            S[4 * c + 3] = *reinterpret_cast<__half2*>(&q.w);
+        }
+    }
+
+    for (int t = 0; t < T; t++) {
+        if (t) __syncthreads();  // previous token's readers are done with sv
+        sv[0][i] = decay_dither(cur.w, t0 + t);
+        sv[1][i] = cur.k;
+        sv[2][i] = cur.a;
+        sv[3][i] = cur.b;
+        sv[4][i] = cur.r;
+        const __half vv = cur.v;
+        __syncthreads();
+        const size_t yidx = idx;
+        if (t + 1 < T) {  // prefetch the next token under this token's math
+            idx += C;
+            cur.r = r_[idx]; cur.w = w_[idx]; cur.k = k_[idx]; cur.v = v_[idx]; cur.a = a_[idx]; cur.b = b_[idx];
+        }
+        const int4* wv = reinterpret_cast<const int4*>(sv[0]);
+        const int4* kv = reinterpret_cast<const int4*>(sv[1]);
+        const int4* av = reinterpret_cast<const int4*>(sv[2]);
+        const int4* bv = reinterpret_cast<const int4*>(sv[3]);
+        const int4* rv = reinterpret_cast<const int4*>(sv[4]);
+
+        // sa_i = sum_j a_j * S_ij on the pre-update state: one half2 fma chain, lo = even j, hi = odd j (.cu:65-70)
+        __half2 acc = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            int4 q = av[c];
+            const __half2* p = reinterpret_cast<const __half2*>(&q);
+#pragma unroll
+            for (int u = 0; u < 4; u++) acc = __hfma2(p[u], S[4 * c + u], acc);
+        }
+        const __half sa = __hadd_rn(__low2half(acc), __high2half(acc));
+        const __half2 sa2 = __half2half2(sa);
+        const __half2 vv2 = __half2half2(vv);
+
+        // S_ij <- S_ij + fma(sa, b_j, fma(S_ij, w~_j, k_j * v_i)) ; y_i = sum_j S_ij(new) * r_j   (.cu:72-81)
+        acc = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            int4 qw = wv[c], qk = kv[c], qb = bv[c], qr = rv[c];
+            const __half2* pw = reinterpret_cast<const __half2*>(&qw);
+            const __half2* pk = reinterpret_cast<const __half2*>(&qk);
+            const __half2* pb = reinterpret_cast<const __half2*>(&qb);
+            const __half2* pr = reinterpret_cast<const __half2*>(&qr);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                __half2 s = S[4 * c + u];
+                __half2 d = __hmul2_rn(pk[u], vv2);
+                d = __hfma2(s, pw[u], d);
+                d = __hfma2(sa2, pb[u], d);
+                s = __hadd2_rn(s, d);
+                S[4 * c + u] = s;
+                acc = __hfma2(s, pr[u], acc);
+            }
+        }
+        y_[yidx] = __hadd_rn(__low2half(acc), __high2half(acc));
+    }
+
+    {
+        int4* rowp = reinterpret_cast<int4*>(tile + i * 128);
+        const int sw = i & 7;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            int4 q;
+            q.x = *reinterpret_cast<int*>(&S[4 * c + 0]);
+            q.y = *reinterpret_cast<int*>(&S[4 * c + 1]);
+            q.z = *reinterpret_cast<int*>(&S[4 * c + 2]);
+            q.w = *reinterpret_cast<int*>(&S[4 * c + 3]);
+            rowp[c ^ sw] = q;
+        }
+    }
+    fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA (async proxy) store
+    __syncthreads();
+    if (i == 0) {
+        tma_store_2d(&tm_state, 0, row0, tile);
+        tma_store_commit();
+        tma_store_wait_read<0>();  // smem must stay valid until the bulk store has read it
+    }
+}
+
+}  // namespace
+
+int wkv7_make_state_tmap(CUtensorMap* tm, const void* state, int n_slots, int H, long state_slot_stride) {
+    if (state_slot_stride % HS != 0 || n_slots < 1) return B200_ERR_BAD_ARG;
+    const uint64_t rows_per_slot = (uint64_t)state_slot_stride / HS;
+    const uint64_t rows = (uint64_t)(n_slots - 1) * rows_per_slot + (uint64_t)H * HS;
+    return make_tmap_2d_f16(tm, state, rows, HS, HS * 2, HS, HS, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_wkv7_forward_seq(int B, int T, int C, int H, void* state, long state_slot_stride, int n_slots,
+                                     const void* r, const void* w, const void* k, const void* v, const void* a,
+                                     const void* b, void* y, const int* elapsed_t, const int* slot_idx, void* stream) {
+    if (B < 0 || T < 0 || H <= 0 || H * HS != C) return B200_ERR_BAD_ARG;  // reference: assert(H*_N_ == C), .cu:314
+    if (B == 0 || T == 0) return 0;
+    if (!slot_idx) n_slots = B;
+    if ((reinterpret_cast<uintptr_t>(state) & 15) != 0) return B200_ERR_BAD_ARG;
+    CUtensorMap tm;
+    int rc = wkv7_make_state_tmap(&tm, state, n_slots, H, state_slot_stride);
+    if (rc) return rc;
+    wkv7_seq_kernel<<<B * H, HS, 0, static_cast<cudaStream_t>(stream)>>>(
+        tm, T, C, H, (int)(state_slot_stride / HS), static_cast<const __half*>(r), static_cast<const __half*>(w),
+        static_cast<const __half*>(k), static_cast<const __half*>(v), static_cast<const __half*>(a),
+        static_cast<const __half*>(b), static_cast<__half*>(y), elapsed_t, slot_idx);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int b200_wkv7_forward_one(int B, int C, int H, void* state, long state_slot_stride, int n_slots, const void* r,
+                                     const void* w, const void* k, const void* v, const void* a, const void* b, void* y,
+                                     const int* elapsed_t, const int* slot_idx, void* stream) {
+    return b200_wkv7_forward_seq(B, 1, C, H, state, state_slot_stride, n_slots, r, w, k, v, a, b, y, elapsed_t, slot_idx,
+                                 stream);
+}
+
+extern "C" int b200_abi_version(void) { return 1; }

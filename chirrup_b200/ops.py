@@ -1,0 +1,116 @@
+"""Operator layer: torch tensors in, C-ABI calls out.  Mirrors the reference's op surface
+(``torch.ops.rwkv7_state_fwd_fp16.{forward_seq,forward_one,spmv_forward}``, ``/root/reference/Albatross/rwkv7.py:61-160``)
+plus the dense linear op.  torch is used for device memory and the current stream only.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+HEAD = 64
+EPI_NONE, EPI_TANH, EPI_SIGMOID, EPI_RELU_SQ, EPI_RESADD = 0, 1, 2, 3, 4
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _req(t: torch.Tensor, name: str, dtype=torch.float16) -> None:
+    if not t.is_cuda:
+        raise _lib.B200Error(f"{name}: chirrup_b200 has no CPU path; got a {t.device} tensor")
+    if t.dtype != dtype:
+        raise TypeError(f"{name}: expected {dtype}, got {t.dtype}")
+
+
+def wkv7_forward_seq(state: torch.Tensor, r, w, k, v, a, b, elapsed_t: torch.Tensor,
+                     slot_idx: Optional[torch.Tensor] = None, y: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``RWKV7_BATCH_OP`` / ``forward_seq`` (reference ``Albatross/rwkv7.py:144-160``): r..b are (B,T,C) fp16, ``state`` is
+    (n_slots,H,64,64) fp16 (a B-axis view is fine) updated in place, ``elapsed_t`` int32 (B,).  Returns y (B,T,C)."""
+    B, T, C = r.shape
+    H = C // HEAD
+    for n, t in (("state", state), ("r", r), ("w", w), ("k", k), ("v", v), ("a", a), ("b", b)):
+        _req(t, n)
+    _req(elapsed_t, "elapsed_t", torch.int32)
+    if state.dim() != 4 or tuple(state.shape[1:]) != (H, HEAD, HEAD) or not state[0].is_contiguous():
+        raise ValueError(f"state must be (n_slots,{H},64,64) with contiguous slots, got {tuple(state.shape)}")
+    ins = [t if t.is_contiguous() else t.contiguous() for t in (r, w, k, v, a, b)]
+    if y is None:
+        y = torch.empty((B, T, C), dtype=torch.float16, device=r.device)
+    et = elapsed_t.reshape(-1)
+    if et.numel() != B:
+        raise ValueError("elapsed_t must have B elements")
+    et = et if et.is_contiguous() else et.contiguous()
+    n_slots = state.shape[0]
+    sp = 0
+    if slot_idx is not None:
+        _req(slot_idx, "slot_idx", torch.int32)
+        sp = slot_idx.data_ptr()
+    elif n_slots < B:
+        raise ValueError("state has fewer slots than sequences")
+    stride = state.stride(0) if n_slots > 1 else C * HEAD
+    rc = _lib.lib().b200_wkv7_forward_seq(B, T, C, H, state.data_ptr(), stride, n_slots, *[t.data_ptr() for t in ins],
+                                          y.data_ptr(), et.data_ptr(), sp, _stream(r))
+    _lib.check(rc, "b200_wkv7_forward_seq")
+    return y
+
+
+def wkv7_forward_one(state, r, w, k, v, a, b, elapsed_t, slot_idx=None) -> torch.Tensor:
+    """``RWKV7_ONE_OP`` / ``RWKV7_ONE_BATCH_OP`` (``Albatross/rwkv7.py:99-141``): inputs (B,C) or (C,)."""
+    shp = r.shape
+    C = shp[-1]
+    H = C // HEAD
+    B = 1 if r.dim() == 1 else shp[0]
+    y = wkv7_forward_seq(state.view(-1, H, HEAD, HEAD), *(t.reshape(B, 1, C) for t in (r, w, k, v, a, b)),
+                         elapsed_t.reshape(-1), slot_idx)
+    return y.view(shp)
+
+
+def spmv_forward(vec: torch.Tensor, mat: torch.Tensor) -> torch.Tensor:
+    """``SPMV_OP`` / ``rwkv_mm_sparsity`` (``Albatross/rwkv7.py:61-87``): vec (D,), mat (D,C) -> (C,)."""
+    _req(vec, "vec")
+    _req(mat, "mat")
+    D, C = mat.shape
+    out = torch.empty((C,), dtype=torch.float16, device=vec.device)
+    rc = _lib.lib().b200_spmv_forward(D, C, vec.contiguous().data_ptr(), mat.contiguous().data_ptr(), out.data_ptr(),
+                                      _stream(vec))
+    _lib.check(rc, "b200_spmv_forward")
+    return out
+
+
+_ws = {}
+
+
+def _workspace(dev: torch.device, M: int, N: int) -> torch.Tensor:
+    need = _lib.lib().b200_linear_workspace_bytes(M, N)
+    ws = _ws.get(dev)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros((max(need, 1 << 20),), dtype=torch.uint8, device=dev)
+        _ws[dev] = ws
+    return ws
+
+
+def linear(x: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor] = None, epilogue: int = EPI_NONE,
+           residual: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``F.linear(x, W, bias)`` with a fused epilogue: x (..., K) fp16, W (N, K) fp16 -> (..., N) fp16 on tcgen05."""
+    _req(x, "x")
+    _req(W, "W")
+    K = x.shape[-1]
+    N = W.shape[0]
+    x2 = x.reshape(-1, K)
+    if x2.stride(-1) != 1:
+        x2 = x2.contiguous()
+    if W.stride(-1) != 1:
+        raise ValueError("W must be K-major (row-major (N,K))")
+    M = x2.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float16, device=x.device)
+    ws = _workspace(x.device, M, N)
+    rc = _lib.lib().b200_linear_f16(M, N, K, x2.data_ptr(), x2.stride(0), W.data_ptr(), W.stride(0), out.data_ptr(),
+                                    out.stride(0), bias.data_ptr() if bias is not None else 0,
+                                    residual.data_ptr() if residual is not None else 0, epilogue, ws.data_ptr(),
+                                    ws.numel(), _stream(x))
+    _lib.check(rc, "b200_linear_f16")
+    return out.view(*x.shape[:-1], N)

@@ -1,0 +1,112 @@
+"""GPU parity of the tcgen05 linear layer (C ABI b200_linear_f16) against a plain PyTorch fp32 reference of the same op.
+Tolerance: fp32 accumulation + one fp16 rounding on both sides -> results agree to 1 fp16 ulp (rtol 2e-3) except for
+summation-order effects, bounded by atol 2e-3 * sqrt(K)/32 on O(1) outputs."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(x, W, bias, epi, res):
+    from chirrup_b200 import ops
+
+    acc = x.float() @ W.float().t()
+    h = lambda t: t.half().float()
+    if epi == ops.EPI_NONE:
+        return (acc + (bias.float() if bias is not None else 0)).half()
+    if epi == ops.EPI_TANH:
+        return torch.tanh(h(acc + (bias.float() if bias is not None else 0))).half()
+    if epi == ops.EPI_SIGMOID:
+        return torch.sigmoid(h(acc + (bias.float() if bias is not None else 0))).half()
+    if epi == ops.EPI_RELU_SQ:
+        return (torch.relu(h(acc)) ** 2).half()
+    return (res.float() + h(acc)).half()
+
+
+SHAPES = [
+    (1, 128, 64), (3, 8, 8), (64, 256, 128), (128, 128, 4096), (129, 136, 72), (256, 4096, 4096), (256, 96, 4096),
+    (256, 4096, 96), (256, 480, 2048), (200, 2048, 480), (256, 16384, 2048), (256, 2048, 8192), (700, 768, 768),
+    (64, 65536, 768), (17, 1024, 3072),
+]
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_linear_plain(M, N, K):
+    from chirrup_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(M * 31 + N * 7 + K)
+    x = (torch.randn(M, K, generator=g, device="cuda")).half()
+    W = (torch.randn(N, K, generator=g, device="cuda") * K ** -0.5).half()
+    y = ops.linear(x, W)
+    torch.cuda.synchronize()
+    ref = _ref(x, W, None, ops.EPI_NONE, None)
+    assert y.shape == (M, N)
+    assert torch.allclose(y.float(), ref.float(), rtol=2e-3, atol=2e-3), (y.float() - ref.float()).abs().max().item()
+
+
+@pytest.mark.parametrize("epi", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("M,N,K", [(256, 512, 1024), (37, 264, 200), (256, 2048, 2048)])
+def test_linear_epilogues(epi, M, N, K):
+    from chirrup_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(epi * 100 + M)
+    x = torch.randn(M, K, generator=g, device="cuda").half()
+    W = (torch.randn(N, K, generator=g, device="cuda") * K ** -0.5).half()
+    bias = torch.randn(N, generator=g, device="cuda").half() if epi in (0, 1, 2) else None
+    res = torch.randn(M, N, generator=g, device="cuda").half() if epi == 4 else None
+    y = ops.linear(x, W, bias, epi, res)
+    torch.cuda.synchronize()
+    ref = _ref(x, W, bias, epi, res)
+    assert torch.allclose(y.float(), ref.float(), rtol=3e-3, atol=3e-3), (y.float() - ref.float()).abs().max().item()
+
+
+def test_linear_inplace_residual_and_determinism():
+    from chirrup_b200 import ops
+
+    M, N, K = 256, 1024, 4096
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randn(M, K, generator=g, device="cuda").half()
+    W = (torch.randn(N, K, generator=g, device="cuda") * K ** -0.5).half()
+    res = torch.randn(M, N, generator=g, device="cuda").half()
+    ref = _ref(x, W, None, ops.EPI_RESADD, res)
+    outs = []
+    for _ in range(3):
+        buf = res.clone()
+        ops.linear(x, W, None, ops.EPI_RESADD, residual=buf, out=buf)
+        outs.append(buf)
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])   # split-K reduction order is fixed
+    assert torch.allclose(outs[0].float(), ref.float(), rtol=3e-3, atol=3e-3)
+
+
+def test_linear_strided_rows_and_empty():
+    from chirrup_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(4)
+    big = torch.randn(40, 3, 256, generator=g, device="cuda").half()
+    x = big[:, 1, :]                       # row pitch 768
+    W = (torch.randn(64, 256, generator=g, device="cuda") / 16).half()
+    y = ops.linear(x, W)
+    assert torch.allclose(y.float(), (x.float() @ W.float().t()), rtol=3e-3, atol=3e-3)
+    assert ops.linear(x[:0], W).shape == (0, 64)
+
+
+def test_spmv_matches_exact_product():
+    """b200_spmv_forward vs the C oracle's exact product (oracle/wkv7_oracle.c: wkv7_oracle_spmv): fp32 accumulation in a
+    fixed order vs double -> equal to 1 fp16 ulp; run-to-run bit-identical (the reference's fp16 atomics are not)."""
+    from chirrup_b200 import ops
+    from oracle import rwkv7_oracle as O
+
+    D, C = 3072, 768
+    g = torch.Generator().manual_seed(8)
+    vec = torch.relu(torch.randn(D, generator=g) - 0.8) ** 2
+    vec = vec.half()
+    mat = (torch.randn(D, C, generator=g) * 0.05).half()
+    want = O.spmv_cpu(vec, mat)
+    a = ops.spmv_forward(vec.cuda(), mat.cuda())
+    b = ops.spmv_forward(vec.cuda(), mat.cuda())
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)
+    assert torch.allclose(a.cpu().float(), want.float(), rtol=2e-3, atol=1e-4)
+    z = ops.spmv_forward(torch.zeros(D, dtype=torch.float16, device="cuda"), mat.cuda())
+    assert torch.count_nonzero(z) == 0
