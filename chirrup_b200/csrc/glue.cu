@@ -1,0 +1,255 @@
+// Elementwise / small-reduction kernels of the RWKV-7 step ("the glue"): each one replaces a chain of ATen launches of the
+// reference model (/root/reference/Albatross/rwkv7.py) and keeps its per-op fp16 rounding (ATen computes each half op in fp32
+// and rounds the result to fp16 — so does every step below; `hr()` is that rounding).
+//
+//   embed_gather      emb[idx]                                                        rwkv7.py:507
+//   ln_shift_mix<N>   LayerNorm -> token shift -> N lerps (+ new shift state)         rwkv7.py:523, :621-623 / :533, :675-677
+//   tmix_prep         kk normalise, k/v mixing, a = -kk, b = kk*a                     rwkv7.py:632-637
+//   tmix_post         GroupNorm(eps 64e-5) + bonus (r.k.r_k) v + gate                 rwkv7.py:647-649
+//   ln_rows           ln_out on the selected rows                                     rwkv7.py:546-548
+//   add_elapsed       state[2] += T                                                   rwkv7.py:552
+#include "common.cuh"
+#include "glue.h"
+
+namespace b200 {
+namespace {
+
+DEVI float hr(float x) { return __half2float(__float2half_rn(x)); }
+
+struct H8 {
+    float f[8];
+};
+DEVI H8 ld8(const __half* p) {
+    int4 q = *reinterpret_cast<const int4*>(p);
+    const __half* h = reinterpret_cast<const __half*>(&q);
+    H8 o;
+#pragma unroll
+    for (int e = 0; e < 8; e++) o.f[e] = __half2float(h[e]);
+    return o;
+}
+DEVI void st8(__half* p, const H8& v) {
+    int4 q;
+    __half* h = reinterpret_cast<__half*>(&q);
+#pragma unroll
+    for (int e = 0; e < 8; e++) h[e] = __float2half_rn(v.f[e]);
+    *reinterpret_cast<int4*>(p) = q;
+}
+
+// Block-wide sum of one float per thread (blockDim.x multiple of 32, <= 1024). `red` holds 33 floats.
+DEVI float block_sum(float v, float* red) {
+    v = warp_sum(v);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    __syncthreads();  // protect `red` from the previous use
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+        float t = lane < nw ? red[lane] : 0.f;
+        t = warp_sum(t);
+        if (lane == 0) red[32] = t;
+    }
+    __syncthreads();
+    return red[32];
+}
+
+// LayerNorm of one row held as 8 values per active thread; fp32 statistics (two-pass), output rounded to fp16.
+DEVI H8 layer_norm8(const H8& x, bool active, int C, const __half* w, const __half* b, int c0, float eps, float* red) {
+    float s = 0.f;
+    if (active) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) s += x.f[e];
+    }
+    const float mean = block_sum(s, red) / (float)C;
+    float q = 0.f;
+    if (active) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            float d = x.f[e] - mean;
+            q += d * d;
+        }
+    }
+    const float var = block_sum(q, red) / (float)C;
+    const float rstd = 1.0f / sqrtf(var + eps);
+    H8 o;
+    if (active) {
+        H8 ww = ld8(w + c0), bb = ld8(b + c0);
+#pragma unroll
+        for (int e = 0; e < 8; e++) o.f[e] = hr((x.f[e] - mean) * rstd * ww.f[e] + bb.f[e]);
+    }
+    return o;
+}
+
+__global__ void embed_gather_kernel(int M, int C, const int* __restrict__ tokens, const __half* __restrict__ emb,
+                                    __half* __restrict__ x) {
+    const int m = blockIdx.x;
+    const __half* src = emb + (size_t)tokens[m] * C;
+    __half* dst = x + (size_t)m * C;
+    for (int c = threadIdx.x * 8; c < C; c += blockDim.x * 8)
+        *reinterpret_cast<int4*>(dst + c) = __ldg(reinterpret_cast<const int4*>(src + c));
+}
+
+// One CTA per (sequence b, token t) row.  cur = LN(x[b,t]); prev = t ? LN(x[b,t-1]) : shift_state[b];
+// out_n = cur + (prev - cur) * mix_n.  The t == 0 CTA also owns the shift state of its sequence: it reads the old value and
+// afterwards stores LN(x[b,T-1]) — no other CTA touches that row, so there is no ordering hazard for T > 1.
+template <int NMIX>
+__global__ void __launch_bounds__(1024) ln_shift_mix_kernel(int T, int C, const __half* __restrict__ x,
+                                                            const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
+                                                            __half* __restrict__ shift, long shift_stride,
+                                                            const int* __restrict__ slot_idx, MixPtrs<NMIX> mp) {
+    __shared__ float red[33];
+    const int m = blockIdx.x;
+    const int b = m / T, t = m - b * T;
+    const int c0 = threadIdx.x * 8;
+    const bool active = c0 < C;
+    const __half* xrow = x + (size_t)m * C;
+    H8 xv;
+    if (active) xv = ld8(xrow + c0);
+    const H8 cur = layer_norm8(xv, active, C, ln_w, ln_b, c0, 1e-5f, red);
+    __half* srow = shift + (size_t)(slot_idx ? slot_idx[b] : b) * shift_stride;
+    H8 prev;
+    if (t > 0) {
+        H8 pv;
+        if (active) pv = ld8(xrow - C + c0);
+        prev = layer_norm8(pv, active, C, ln_w, ln_b, c0, 1e-5f, red);
+    } else {
+        if (active) prev = ld8(srow + c0);
+        H8 last = cur;
+        if (T > 1) {
+            H8 lv;
+            if (active) lv = ld8(xrow + (size_t)(T - 1) * C + c0);
+            last = layer_norm8(lv, active, C, ln_w, ln_b, c0, 1e-5f, red);
+        }
+        if (active) st8(srow + c0, last);
+    }
+    if (!active) return;
+    H8 dx;
+#pragma unroll
+    for (int e = 0; e < 8; e++) dx.f[e] = hr(prev.f[e] - cur.f[e]);
+#pragma unroll
+    for (int n = 0; n < NMIX; n++) {
+        const H8 mx = ld8(mp.mix[n] + c0);
+        H8 o;
+#pragma unroll
+        for (int e = 0; e < 8; e++) o.f[e] = hr(cur.f[e] + hr(dx.f[e] * mx.f[e]));
+        st8(mp.out[n] + (size_t)m * C + c0, o);
+    }
+}
+
+// LayerNorm of selected rows: out[i] = LN(x[i*row_step + row_off]).
+__global__ void __launch_bounds__(1024) ln_rows_kernel(int C, const __half* __restrict__ x, long row_step, long row_off,
+                                                       const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
+                                                       __half* __restrict__ out) {
+    __shared__ float red[33];
+    const int c0 = threadIdx.x * 8;
+    const bool active = c0 < C;
+    const __half* xrow = x + ((size_t)blockIdx.x * row_step + row_off) * C;
+    H8 xv;
+    if (active) xv = ld8(xrow + c0);
+    const H8 o = layer_norm8(xv, active, C, ln_w, ln_b, c0, 1e-5f, red);
+    if (active) st8(out + (size_t)blockIdx.x * C + c0, o);
+}
+
+__global__ void add_elapsed_kernel(int B, int T, int* __restrict__ elapsed) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < B) elapsed[i] += T;
+}
+
+DEVI float2 ld2(const __half* p) { return __half22float2(*reinterpret_cast<const __half2*>(p)); }
+DEVI void st2(__half* p, float x, float y) { *reinterpret_cast<__half2*>(p) = __floats2half2_rn(x, y); }
+
+// One warp per (token m, head h); lane holds channels h*64 + 2*lane, +1.                         rwkv7.py:632-637
+__global__ void __launch_bounds__(128) tmix_prep_kernel(TmixPrepArgs p) {
+    const int H = p.C >> 6;
+    const int gw = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (gw >= p.M * H) return;
+    const int lane = threadIdx.x & 31;
+    const int m = gw / H, h = gw - m * H;
+    const int c = h * 64 + lane * 2;
+    const size_t i = (size_t)m * p.C + c;
+    const float2 k = ld2(p.k + i), a = ld2(p.a + i), kk_w = ld2(p.k_k + c), ka_w = ld2(p.k_a + c);
+    // kk = normalize(k * k_k) per head: norm accumulated in fp32 and rounded to fp16 (x.norm() on a half tensor), then divided
+    const float q0 = hr(k.x * kk_w.x), q1 = hr(k.y * kk_w.y);
+    const float nrm = hr(sqrtf(warp_sum(q0 * q0 + q1 * q1)));
+    const float kk0 = hr(q0 / nrm), kk1 = hr(q1 / nrm);
+    // k = k * (1 + (a - 1) * k_a)
+    const float k0 = hr(k.x * hr(1.0f + hr(hr(a.x - 1.0f) * ka_w.x)));
+    const float k1 = hr(k.y * hr(1.0f + hr(hr(a.y - 1.0f) * ka_w.y)));
+    st2(p.k_out + i, k0, k1);
+    st2(p.a_out + i, -kk0, -kk1);
+    st2(p.b_out + i, hr(kk0 * a.x), hr(kk1 * a.y));
+    if (p.v_first != nullptr) {  // v = v + (v_first - v) * sigmoid(...)
+        const float2 v = ld2(p.v + i), vf = ld2(p.v_first + i), gt = ld2(p.vgate + i);
+        st2(p.v_out + i, hr(v.x + hr(hr(vf.x - v.x) * gt.x)), hr(v.y + hr(hr(vf.y - v.y) * gt.y)));
+    }
+}
+
+// One warp per (token, head): GroupNorm over the head's 64 outputs, bonus term, gate.               rwkv7.py:647-649
+__global__ void __launch_bounds__(128) tmix_post_kernel(TmixPostArgs p) {
+    const int H = p.C >> 6;
+    const int gw = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (gw >= p.M * H) return;
+    const int lane = threadIdx.x & 31;
+    const int m = gw / H, h = gw - m * H;
+    const int c = h * 64 + lane * 2;
+    const size_t i = (size_t)m * p.C + c;
+    const float2 y = ld2(p.y + i);
+    const float mean = warp_sum(y.x + y.y) * (1.0f / 64.0f);
+    const float d0 = y.x - mean, d1 = y.y - mean;
+    const float var = warp_sum(d0 * d0 + d1 * d1) * (1.0f / 64.0f);
+    const float rstd = 1.0f / sqrtf(var + 64e-5f);
+    const float2 gw_ = ld2(p.ln_w + c), gb_ = ld2(p.ln_b + c);
+    const float n0 = hr(d0 * rstd * gw_.x + gb_.x), n1 = hr(d1 * rstd * gw_.y + gb_.y);
+    const float2 r = ld2(p.r + i), k = ld2(p.k + i), v = ld2(p.v + i), g = ld2(p.g + i), rk = ld2(p.r_k + c);
+    const float s = hr(warp_sum(hr(hr(r.x * k.x) * rk.x) + hr(hr(r.y * k.y) * rk.y)));
+    const float o0 = hr(n0 + hr(s * v.x)), o1 = hr(n1 + hr(s * v.y));
+    st2(p.out + i, hr(o0 * g.x), hr(o1 * g.y));
+}
+
+int ln_threads(int C) {
+    int t = (C / 8 + 31) / 32 * 32;
+    return t < 32 ? 32 : t;
+}
+
+}  // namespace
+
+int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __half* x, cudaStream_t s) {
+    if (M <= 0) return 0;
+    embed_gather_kernel<<<M, 128, 0, s>>>(M, C, tokens, emb, x);
+    return (int)cudaGetLastError();
+}
+int launch_ln_shift_mix6(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
+                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s) {
+    if (B * T <= 0) return 0;
+    ln_shift_mix_kernel<6><<<B * T, ln_threads(C), 0, s>>>(T, C, x, ln_w, ln_b, shift, shift_stride, slot_idx, mp);
+    return (int)cudaGetLastError();
+}
+int launch_ln_shift_mix1(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
+                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s) {
+    if (B * T <= 0) return 0;
+    ln_shift_mix_kernel<1><<<B * T, ln_threads(C), 0, s>>>(T, C, x, ln_w, ln_b, shift, shift_stride, slot_idx, mp);
+    return (int)cudaGetLastError();
+}
+int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off, const __half* ln_w, const __half* ln_b,
+                   __half* out, cudaStream_t s) {
+    if (rows <= 0) return 0;
+    ln_rows_kernel<<<rows, ln_threads(C), 0, s>>>(C, x, row_step, row_off, ln_w, ln_b, out);
+    return (int)cudaGetLastError();
+}
+int launch_add_elapsed(int B, int T, int* elapsed, cudaStream_t s) {
+    if (B <= 0) return 0;
+    add_elapsed_kernel<<<(B + 127) / 128, 128, 0, s>>>(B, T, elapsed);
+    return (int)cudaGetLastError();
+}
+int launch_tmix_prep(const TmixPrepArgs& a, cudaStream_t s) {
+    const int warps = a.M * (a.C >> 6);
+    if (warps <= 0) return 0;
+    tmix_prep_kernel<<<(warps + 3) / 4, 128, 0, s>>>(a);
+    return (int)cudaGetLastError();
+}
+int launch_tmix_post(const TmixPostArgs& a, cudaStream_t s) {
+    const int warps = a.M * (a.C >> 6);
+    if (warps <= 0) return 0;
+    tmix_post_kernel<<<(warps + 3) / 4, 128, 0, s>>>(a);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200

@@ -1,0 +1,45 @@
+// Internal launch interface of the glue kernels and of the linear / WKV launchers used by the model step (model.cu).
+#pragma once
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+namespace b200 {
+
+template <int NMIX>
+struct MixPtrs {
+    const __half* mix[NMIX];  // lerp coefficients (C)
+    __half* out[NMIX];        // outputs (M, C)
+};
+
+int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __half* x, cudaStream_t s);
+int launch_ln_shift_mix6(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
+                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s);
+int launch_ln_shift_mix1(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
+                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s);
+int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off, const __half* ln_w, const __half* ln_b,
+                   __half* out, cudaStream_t s);
+int launch_add_elapsed(int B, int T, int* elapsed, cudaStream_t s);
+
+struct TmixPrepArgs {
+    int M, C;
+    const __half *k, *v, *a, *vgate, *v_first;  // vgate/v_first == nullptr on layer 0
+    const __half *k_k, *k_a;
+    __half *k_out, *v_out, *a_out, *b_out;
+};
+int launch_tmix_prep(const TmixPrepArgs& a, cudaStream_t s);
+
+struct TmixPostArgs {
+    int M, C;
+    const __half *y, *r, *k, *v, *g;
+    const __half *ln_w, *ln_b, *r_k;
+    __half* out;
+};
+int launch_tmix_post(const TmixPostArgs& a, cudaStream_t s);
+
+// gemm.cu
+int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* W, long ldw, void* out, long ldo,
+                      const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,
+                      cudaStream_t stream);
+
+}  // namespace b200

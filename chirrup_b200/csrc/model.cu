@@ -1,0 +1,188 @@
+// The batched RWKV-7 step as one sequence of sm_100a kernel launches on a caller-supplied stream.
+// Follows RWKV_x070.forward_seq_batch_seperate (/root/reference/Albatross/rwkv7.py:555-563 -> _pre :503-509,
+// _layers :511-538, _post :540-553) with TMix = rwkv7.py:618-649 and CMix = :673-679.
+#include <new>
+
+#include "common.cuh"
+#include "glue.h"
+#include "../../include/chirrup_b200.h"
+
+struct b200_model {
+    int L, C, V, H, F, d_w, d_a, d_v, d_g;
+    const __half* gw[4];
+    const __half** lw;  // L * B200_LW_COUNT
+    int last_launches;
+};
+
+namespace b200 {
+namespace {
+
+inline long align_up(long x, long a) { return (x + a - 1) / a * a; }
+
+// Workspace carve-up for M tokens.
+struct Ws {
+    int* counters_and_partials;  // linear workspace
+    long lin_bytes;
+    __half *x, *mix[6], *r, *k, *v, *w, *a, *g, *vg, *k2, *v2, *an, *bn, *y, *yg, *vfirst, *kx, *lora, *hidden, *xo;
+    long total;
+};
+
+Ws carve(const b200_model* m, long M, void* base) {
+    Ws ws;
+    uint8_t* p = static_cast<uint8_t*>(base);
+    long off = 0;
+    auto take = [&](long bytes) {
+        uint8_t* q = p ? p + off : nullptr;
+        off += align_up(bytes, 256);
+        return q;
+    };
+    ws.lin_bytes = b200_linear_workspace_bytes((int)M, m->V);
+    ws.counters_and_partials = reinterpret_cast<int*>(take(ws.lin_bytes));
+    const long mc = M * m->C * 2;
+    __half** bufs[] = {&ws.x,  &ws.mix[0], &ws.mix[1], &ws.mix[2], &ws.mix[3], &ws.mix[4], &ws.mix[5], &ws.r, &ws.k,
+                       &ws.v,  &ws.w,      &ws.a,      &ws.g,      &ws.vg,     &ws.k2,     &ws.v2,     &ws.an, &ws.bn,
+                       &ws.y,  &ws.yg,     &ws.vfirst, &ws.kx,     &ws.xo};
+    for (auto b : bufs) *b = reinterpret_cast<__half*>(take(mc));
+    int dmax = m->d_w;
+    if (m->d_a > dmax) dmax = m->d_a;
+    if (m->d_v > dmax) dmax = m->d_v;
+    if (m->d_g > dmax) dmax = m->d_g;
+    ws.lora = reinterpret_cast<__half*>(take(M * align_up(dmax, 8) * 2));
+    ws.hidden = reinterpret_cast<__half*>(take(M * (long)m->F * 2));
+    ws.total = off;
+    return ws;
+}
+
+}  // namespace
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_model_create(int n_layer, int n_embd, int vocab_size, int d_w, int d_a, int d_v, int d_g,
+                                 const void* const* global_w, const void* const* layer_w, b200_model** out) {
+    if (!out || !global_w || !layer_w || n_layer <= 0 || n_embd <= 0 || (n_embd % 64) || vocab_size <= 0 || (vocab_size & 7))
+        return B200_ERR_BAD_ARG;
+    if (d_w <= 0 || d_a <= 0 || d_v <= 0 || d_g <= 0 || (d_w & 7) || (d_a & 7) || (d_v & 7) || (d_g & 7)) return B200_ERR_BAD_ARG;
+    b200_model* m = new (std::nothrow) b200_model();
+    if (!m) return B200_ERR_BAD_ARG;
+    m->L = n_layer; m->C = n_embd; m->V = vocab_size; m->H = n_embd / 64; m->F = 4 * n_embd;
+    m->d_w = d_w; m->d_a = d_a; m->d_v = d_v; m->d_g = d_g;
+    for (int i = 0; i < 4; i++) m->gw[i] = static_cast<const __half*>(global_w[i]);
+    m->lw = new (std::nothrow) const __half*[(size_t)n_layer * B200_LW_COUNT];
+    for (long i = 0; i < (long)n_layer * B200_LW_COUNT; i++) m->lw[i] = static_cast<const __half*>(layer_w[i]);
+    m->last_launches = 0;
+    *out = m;
+    return 0;
+}
+
+extern "C" void b200_model_destroy(b200_model* m) {
+    if (!m) return;
+    delete[] m->lw;
+    delete m;
+}
+
+extern "C" long b200_model_workspace_bytes(const b200_model* m, int max_tokens) {
+    if (!m || max_tokens < 0) return B200_ERR_BAD_ARG;
+    return carve(m, max_tokens < 1 ? 1 : max_tokens, nullptr).total;
+}
+
+extern "C" int b200_model_last_launch_count(const b200_model* m) { return m ? m->last_launches : 0; }
+
+extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens, void* state0, long s0_layer_stride,
+                                  long s0_which_stride, void* state1, long s1_layer_stride, int n_slots, int* elapsed,
+                                  const int* slot_idx, void* logits, int full_output, void* workspace, long workspace_bytes,
+                                  void* stream_) {
+    if (!m || B < 0 || T < 0) return B200_ERR_BAD_ARG;
+    if (B == 0 || T == 0) return 0;
+    cudaStream_t st = static_cast<cudaStream_t>(stream_);
+    const int C = m->C, H = m->H, F = m->F, L = m->L;
+    const long M = (long)B * T;
+    Ws ws = carve(m, M, workspace);
+    if (!workspace || workspace_bytes < ws.total) return B200_ERR_WORKSPACE;
+    if (!slot_idx) n_slots = B;
+    int n = 0, rc = 0;
+#define RUN(call)            \
+    do {                     \
+        rc = (call);         \
+        n++;                 \
+        if (rc) return rc;   \
+    } while (0)
+    auto lin = [&](long rows, int N, int K, const __half* A, const __half* W, __half* out, const __half* bias,
+                   const __half* res, int epi) {
+        return linear_f16_launch((int)rows, N, K, A, K, W, K, out, N, bias, res, epi, ws.counters_and_partials, ws.lin_bytes, st);
+    };
+    __half* s0 = static_cast<__half*>(state0);
+    __half* s1 = static_cast<__half*>(state1);
+
+    RUN(launch_embed_gather((int)M, C, tokens, m->gw[0], ws.x, st));
+    for (int l = 0; l < L; l++) {
+        const __half** w = m->lw + (size_t)l * B200_LW_COUNT;
+        // ---- TMix
+        MixPtrs<6> mp;
+        for (int i = 0; i < 6; i++) {
+            mp.mix[i] = w[B200_LW_X_R + i];
+            mp.out[i] = ws.mix[i];
+        }
+        __half *xr = ws.mix[0], *xw = ws.mix[1], *xk = ws.mix[2], *xv = ws.mix[3], *xa = ws.mix[4], *xg = ws.mix[5];
+        RUN(launch_ln_shift_mix6(B, T, C, ws.x, w[B200_LW_LN1_W], w[B200_LW_LN1_B], s0 + l * s0_layer_stride, C, slot_idx, mp, st));
+        __half* vbuf = (l == 0) ? ws.vfirst : ws.v;  // layer 0: v_first = v (rwkv7.py:636)
+        RUN(lin(M, C, C, xr, w[B200_LW_RECEPTANCE], ws.r, nullptr, nullptr, B200_EPI_NONE));
+        RUN(lin(M, C, C, xk, w[B200_LW_KEY], ws.k, nullptr, nullptr, B200_EPI_NONE));
+        RUN(lin(M, C, C, xv, w[B200_LW_VALUE], vbuf, nullptr, nullptr, B200_EPI_NONE));
+        RUN(lin(M, m->d_w, C, xw, w[B200_LW_W1], ws.lora, nullptr, nullptr, B200_EPI_TANH));
+        RUN(lin(M, C, m->d_w, ws.lora, w[B200_LW_W2], ws.w, w[B200_LW_W0], nullptr, B200_EPI_NONE));
+        RUN(lin(M, m->d_a, C, xa, w[B200_LW_A1], ws.lora, nullptr, nullptr, B200_EPI_NONE));
+        RUN(lin(M, C, m->d_a, ws.lora, w[B200_LW_A2], ws.a, w[B200_LW_A0], nullptr, B200_EPI_SIGMOID));
+        RUN(lin(M, m->d_g, C, xg, w[B200_LW_G1], ws.lora, nullptr, nullptr, B200_EPI_SIGMOID));
+        RUN(lin(M, C, m->d_g, ws.lora, w[B200_LW_G2], ws.g, nullptr, nullptr, B200_EPI_NONE));
+        if (l > 0) {
+            RUN(lin(M, m->d_v, C, xv, w[B200_LW_V1], ws.lora, nullptr, nullptr, B200_EPI_NONE));
+            RUN(lin(M, C, m->d_v, ws.lora, w[B200_LW_V2], ws.vg, w[B200_LW_V0], nullptr, B200_EPI_SIGMOID));
+        }
+        TmixPrepArgs pa;
+        pa.M = (int)M; pa.C = C;
+        pa.k = ws.k; pa.v = vbuf; pa.a = ws.a;
+        pa.vgate = l > 0 ? ws.vg : nullptr;
+        pa.v_first = l > 0 ? ws.vfirst : nullptr;
+        pa.k_k = w[B200_LW_K_K]; pa.k_a = w[B200_LW_K_A];
+        pa.k_out = ws.k2; pa.v_out = ws.v2; pa.a_out = ws.an; pa.b_out = ws.bn;
+        RUN(launch_tmix_prep(pa, st));
+        const __half* vv = l > 0 ? ws.v2 : ws.vfirst;
+        RUN(b200_wkv7_forward_seq(B, T, C, H, s1 + l * s1_layer_stride, (long)C * 64, n_slots, ws.r, ws.w, ws.k2, vv, ws.an,
+                                  ws.bn, ws.y, elapsed, slot_idx, st));
+        TmixPostArgs po;
+        po.M = (int)M; po.C = C;
+        po.y = ws.y; po.r = ws.r; po.k = ws.k2; po.v = vv; po.g = ws.g;
+        po.ln_w = w[B200_LW_LNX_W]; po.ln_b = w[B200_LW_LNX_B]; po.r_k = w[B200_LW_R_K];
+        po.out = ws.yg;
+        RUN(launch_tmix_post(po, st));
+        RUN(lin(M, C, C, ws.yg, w[B200_LW_OUTPUT], ws.x, nullptr, ws.x, B200_EPI_RESADD));
+        // ---- CMix
+        MixPtrs<1> mc;
+        mc.mix[0] = w[B200_LW_FFN_X_K];
+        mc.out[0] = ws.kx;
+        RUN(launch_ln_shift_mix1(B, T, C, ws.x, w[B200_LW_LN2_W], w[B200_LW_LN2_B], s0 + l * s0_layer_stride + s0_which_stride, C,
+                                 slot_idx, mc, st));
+        RUN(lin(M, F, C, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, nullptr, nullptr, B200_EPI_RELU_SQ));
+        RUN(lin(M, C, F, ws.hidden, w[B200_LW_FFN_VALUE], ws.x, nullptr, ws.x, B200_EPI_RESADD));
+    }
+    if (logits) {
+        if (full_output) {
+            RUN(launch_ln_rows((int)M, C, ws.x, 1, 0, m->gw[1], m->gw[2], ws.xo, st));
+            RUN(lin(M, m->V, C, ws.xo, m->gw[3], static_cast<__half*>(logits), nullptr, nullptr, B200_EPI_NONE));
+        } else {
+            RUN(launch_ln_rows(B, C, ws.x, T, T - 1, m->gw[1], m->gw[2], ws.xo, st));
+            RUN(lin(B, m->V, C, ws.xo, m->gw[3], static_cast<__half*>(logits), nullptr, nullptr, B200_EPI_NONE));
+        }
+    }
+    RUN(launch_add_elapsed(B, T, elapsed, st));
+#undef RUN
+    m->last_launches = n;
+    return 0;
+}
+
+extern "C" int b200_layer_norm_f16(int rows, int C, const void* x, const void* w, const void* b, void* out, void* stream) {
+    if (rows < 0 || C <= 0 || (C & 7) || C > 8192) return B200_ERR_BAD_ARG;
+    return launch_ln_rows(rows, C, static_cast<const __half*>(x), 1, 0, static_cast<const __half*>(w),
+                          static_cast<const __half*>(b), static_cast<__half*>(out), static_cast<cudaStream_t>(stream));
+}

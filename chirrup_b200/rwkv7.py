@@ -1,0 +1,240 @@
+"""Host-side mirror of Albatross's model/state API over the C-ABI library.
+
+Drop-in for ``from Albatross.rwkv7 import RWKV_x070`` (``/root/reference/Albatross/rwkv7.py:164-563``): same constructor
+arguments, attributes, state layout (``generate_zero_state``, ``:224-235``) and ``forward*`` family with the same argument
+meaning, in-place state mutation and fp16 logits.  All arithmetic runs in ``libchirrup_b200.so``; torch only owns device
+memory and the stream.  There is no CPU path: constructing the model without a CUDA device raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import types
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from . import _lib
+
+HEAD_SIZE = 64
+DTYPE = torch.half
+
+# keys transposed at load by the reference (rwkv7.py:217-218).  ffn.value.weight is NOT transposed here: the checkpoint
+# layout (C, 4C) is already the K-major (N, K) layout the tensor-core kernel wants; z[...] exposes the reference view.
+_T_KEYS = ("att.g1", "att.g2", "att.a1", "att.a2", "att.w1", "att.w2", "att.v1", "att.v2")
+
+_LW_ORDER = [
+    "ln1.weight", "ln1.bias", "ln2.weight", "ln2.bias",
+    "att.x_r", "att.x_w", "att.x_k", "att.x_v", "att.x_a", "att.x_g",
+    "att.w0", "att.w1", "att.w2", "att.a0", "att.a1", "att.a2", "att.v0", "att.v1", "att.v2", "att.g1", "att.g2",
+    "att.k_k", "att.k_a", "att.r_k",
+    "att.receptance.weight", "att.key.weight", "att.value.weight", "att.output.weight",
+    "att.ln_x.weight", "att.ln_x.bias",
+    "ffn.x_k", "ffn.key.weight", "ffn.value.weight",
+]
+
+
+def _stream(dev) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+class RWKV_x070:
+    """B200-native RWKV-7 ("x070") inference model with Albatross's interface."""
+
+    def __init__(self, args, auto_load: bool = True, state_dict: Optional[Dict[str, torch.Tensor]] = None,
+                 device: Optional[torch.device] = None):
+        if not torch.cuda.is_available():
+            raise _lib.B200Error("chirrup_b200.RWKV_x070 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.args = args
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self._handle = None
+        self._ws = None
+        self._ws_tokens = 0
+        raw = state_dict if state_dict is not None else torch.load(args.MODEL_NAME + ".pth", map_location="cpu")
+        self.n_head, self.head_size = raw["blocks.0.att.r_k"].shape          # rwkv7.py:173
+        assert self.head_size == HEAD_SIZE
+        args.head_size = self.head_size
+        args.vocab_size, args.n_embd = raw["emb.weight"].shape                # rwkv7.py:174-175
+        args.n_layer = 1 + max(int(k.split(".")[1]) for k in raw if k.startswith("blocks."))
+        self.n_layer, self.n_embd, self.vocab_size = args.n_layer, args.n_embd, args.vocab_size
+        self._raw = raw
+        self.z: Dict[str, torch.Tensor] = {}
+        if auto_load:
+            self.load_weights()
+
+    # ---------------------------------------------------------------- weights
+    def load_weights(self) -> None:
+        """``load_weights_to_device`` + the post-load fixes (rwkv7.py:199-221)."""
+        L = _lib.lib()
+        dev, C = self.device, self.n_embd
+        w: Dict[str, torch.Tensor] = {}
+        for key, t in self._raw.items():
+            if any(s in key for s in _T_KEYS):
+                t = t.t()
+            t = t.squeeze().to(device=dev, dtype=DTYPE)
+            if key.endswith("att.r_k"):
+                t = t.flatten()
+            w[key] = t.contiguous()
+        self._raw = None
+        with torch.cuda.device(dev):
+            # emb <- LayerNorm(emb, ln0)  (rwkv7.py:206), on our own kernel, in place, in row blocks
+            emb = w["emb.weight"]
+            rc = L.b200_layer_norm_f16(emb.shape[0], C, emb.data_ptr(), w["blocks.0.ln0.weight"].data_ptr(),
+                                       w["blocks.0.ln0.bias"].data_ptr(), emb.data_ptr(), _stream(dev))
+            _lib.check(rc, "b200_layer_norm_f16")
+        for s in ("0", "1", "2"):                                             # rwkv7.py:207-209
+            w[f"blocks.0.att.v{s}"] = w[f"blocks.0.att.a{s}"]
+        self._w = w
+        # reference-layout view of the dict (ffn.value.weight as (4C, C))
+        self.z = {k: (v.t() if k.endswith("ffn.value.weight") else v) for k, v in w.items()}
+        g = [w["emb.weight"], w["ln_out.weight"], w["ln_out.bias"], w["head.weight"]]
+        lw = [w[f"blocks.{i}.{name}"] for i in range(self.n_layer) for name in _LW_ORDER]
+        self._keep = g + lw
+        GP = (ctypes.c_void_p * 4)(*[t.data_ptr() for t in g])
+        LP = (ctypes.c_void_p * len(lw))(*[t.data_ptr() for t in lw])
+        d = lambda n: w[f"blocks.0.att.{n}1"].shape[0]
+        h = ctypes.c_void_p()
+        rc = L.b200_model_create(self.n_layer, C, self.vocab_size, d("w"), d("a"), d("v"), d("g"), GP, LP, ctypes.byref(h))
+        _lib.check(rc, "b200_model_create")
+        self._handle = h
+        torch.cuda.synchronize(dev)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_handle", None):
+                _lib.lib().b200_model_destroy(self._handle)
+                self._handle = None
+        except Exception:
+            pass
+
+    def _workspace(self, n_tokens: int) -> torch.Tensor:
+        if self._ws is None or n_tokens > self._ws_tokens:
+            cap = max(n_tokens, 64)
+            need = _lib.lib().b200_model_workspace_bytes(self._handle, cap)
+            self._ws = None
+            self._ws = torch.zeros((need,), dtype=torch.uint8, device=self.device)
+            self._ws_tokens = cap
+        return self._ws
+
+    # ---------------------------------------------------------------- state
+    def generate_zero_state(self, bsz: int) -> List[torch.Tensor]:
+        """rwkv7.py:224-235: bsz >= 1 -> batched layout, 0 -> unbatched (bsz-1 ``forward`` path)."""
+        L, C, H, N, dev = self.n_layer, self.n_embd, self.n_head, self.head_size, self.device
+        if bsz >= 1:
+            return [torch.zeros((L, 2, bsz, C), dtype=DTYPE, device=dev),
+                    torch.zeros((L, bsz, H, N, N), dtype=DTYPE, device=dev),
+                    torch.zeros((bsz,), dtype=torch.int32, device=dev)]
+        return [torch.zeros((L, 2, C), dtype=DTYPE, device=dev),
+                torch.zeros((L, H, N, N), dtype=DTYPE, device=dev),
+                torch.zeros((), dtype=torch.int32, device=dev)]
+
+    # ---------------------------------------------------------------- the step
+    def _step(self, tokens: torch.Tensor, B: int, T: int, state: List[torch.Tensor], full_output: bool,
+              want_logits: bool = True, slot_idx: Optional[torch.Tensor] = None,
+              out: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+        """tokens: int32 device tensor (B*T).  state: batched layout (views allowed)."""
+        s0, s1, s2 = state
+        C, H, V = self.n_embd, self.n_head, self.vocab_size
+        if s0.dtype != DTYPE or s1.dtype != DTYPE or s2.dtype != torch.int32:
+            raise TypeError("state must be [fp16, fp16, int32]")
+        if s0.dim() != 4 or s0.stride(3) != 1 or s0.stride(2) != C:
+            raise ValueError("state[0] must be a B-axis view of an (L,2,B,C) tensor")
+        if s1.dim() != 5 or s1.stride(1) != C * HEAD_SIZE or not s1[0, 0].is_contiguous():
+            raise ValueError("state[1] must be a B-axis view of an (L,B,H,64,64) tensor")
+        if s2.dim() != 1 or (s2.numel() > 1 and s2.stride(0) != 1) or s2.numel() != B:
+            raise ValueError("state[2] must be a contiguous int32 (B,) tensor")
+        n_slots = s1.shape[1]
+        sp = 0
+        if slot_idx is not None:
+            sp = slot_idx.data_ptr()
+        elif n_slots < B:
+            raise ValueError("state has fewer rows than sequences")
+        logits = None
+        if want_logits:
+            rows = B * T if full_output else B
+            logits = out if out is not None else torch.empty((rows, V), dtype=DTYPE, device=self.device)
+        ws = self._workspace(B * T)
+        rc = _lib.lib().b200_model_forward(
+            self._handle, B, T, tokens.data_ptr(), s0.data_ptr(), s0.stride(0), s0.stride(1), s1.data_ptr(), s1.stride(0),
+            n_slots, s2.data_ptr(), sp, logits.data_ptr() if logits is not None else 0, 1 if full_output else 0,
+            ws.data_ptr(), ws.numel(), _stream(self.device))
+        _lib.check(rc, "b200_model_forward")
+        if logits is None:
+            return None
+        return logits.view(B, T, V) if full_output else logits
+
+    def _tokens(self, idxs) -> torch.Tensor:
+        if torch.is_tensor(idxs):
+            return idxs.to(device=self.device, dtype=torch.int32).reshape(-1).contiguous()
+        return torch.tensor(idxs, dtype=torch.int32).reshape(-1).to(self.device, non_blocking=True)
+
+    def forward_seq_batch(self, idxs: Sequence[Sequence[int]], state: List[torch.Tensor], full_output: bool = False):
+        """rwkv7.py:351-382 — rectangular (B,T) token lists, batched state, logits (B,V) or (B,T,V)."""
+        B = len(idxs)
+        T = len(idxs[0]) if B else 0
+        if B == 0:
+            return torch.empty((0, self.vocab_size), dtype=DTYPE, device=self.device)
+        return self._step(self._tokens(idxs), B, T, state, full_output)
+
+    def forward_seq_batch_seperate(self, idxs, state, full_output: bool = False):
+        """rwkv7.py:555-563 (the entry point Chirrup's worker calls, chirrup/worker.py:704, :775)."""
+        return self.forward_seq_batch(idxs, state, full_output)
+
+    def forward_batch_same_length(self, tokens, state, full_output: bool = False):
+        """rwkv7.py:282-285."""
+        assert len(set(len(x) for x in tokens)) == 1, "here all sequences must have the same length"
+        return self.forward_seq_batch(tokens, state, full_output)
+
+    def forward_batch(self, tokens: List[List[int]], state: List[torch.Tensor], full_output: bool = False):
+        """rwkv7.py:250-280 — ragged lengths: step the common prefix of the still-active sequences.  The reference gathers and
+        scatters state rows by fancy indexing; here the kernels address the rows through a slot-index vector instead."""
+        assert isinstance(tokens, list)
+        lengths = [len(x) for x in tokens]
+        if len(set(lengths)) == 1 and not full_output:
+            return self.forward_batch_same_length(tokens, state, full_output)
+        bsz = len(tokens)
+        pos = [0] * bsz
+        V = self.vocab_size
+        out = torch.empty((bsz, V), dtype=DTYPE, device=self.device) if not full_output else \
+            [torch.empty((0, V), dtype=DTYPE, device=self.device) for _ in range(bsz)]
+        while True:
+            active = [i for i in range(bsz) if pos[i] < lengths[i]]
+            if not active:
+                break
+            step = min(lengths[i] - pos[i] for i in active)
+            chunk = [tokens[i][pos[i]:pos[i] + step] for i in active]
+            idx = torch.tensor(active, dtype=torch.int32, device=self.device)
+            elapsed = state[2][idx.long()].contiguous()
+            new = self._step(self._tokens(chunk), len(active), step, [state[0], state[1], elapsed], full_output, slot_idx=idx)
+            state[2][idx.long()] = elapsed
+            for k_, i in enumerate(active):
+                if not full_output:
+                    out[i] = new[k_]
+                else:
+                    out[i] = torch.cat([out[i], new[k_]], dim=0)
+                pos[i] += step
+        return out
+
+    # ---------------------------------------------------------------- bsz-1 API (unbatched state layout)
+    def _batched_view(self, state):
+        return [state[0].unsqueeze(2), state[1].unsqueeze(1), state[2].view(1)]
+
+    def forward(self, idx, state, full_output: bool = False):
+        """rwkv7.py:237-248."""
+        if isinstance(idx, list):
+            if len(idx) > 1:
+                return self.forward_seq(idx, state, full_output)
+            return self.forward_one(idx[0], state)
+        return self.forward_one(idx, state)
+
+    def forward_one(self, idx: int, state):
+        """rwkv7.py:287-316 — one token, unbatched state; returns logits (V,)."""
+        return self._step(self._tokens([int(idx)]), 1, 1, self._batched_view(state), False)[0]
+
+    def forward_seq(self, idx: List[int], state, full_output: bool = False):
+        """rwkv7.py:318-349 — one sequence, unbatched state; logits (V,) or (T,V)."""
+        out = self._step(self._tokens(list(idx)), 1, len(idx), self._batched_view(state), full_output)
+        return out[0]
+
+
+def make_args(model_name: str = "", vocab_size: int = 65536, head_size: int = 64):
+    return types.SimpleNamespace(MODEL_NAME=model_name, vocab_size=vocab_size, head_size=head_size)

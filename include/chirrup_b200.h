@@ -78,6 +78,64 @@ int b200_linear_f16(int M, int N, int K, const void* A, long lda, const void* W,
                     void* stream);
 long b200_linear_workspace_bytes(int max_M, int max_N);
 
+/* out[i,:] = LayerNorm(x[i,:]) * w + b over `rows` contiguous rows of C fp16 (eps 1e-5, fp32 statistics); used at load time
+ * to fold ln0 into the embedding table (Albatross/rwkv7.py:206).  out may alias x. */
+int b200_layer_norm_f16(int rows, int C, const void* x, const void* w, const void* b, void* out, void* stream);
+
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * The whole batched step: RWKV_x070.forward_seq_batch_seperate (Albatross/rwkv7.py:555-563 -> :503-553), i.e.
+ * embedding gather, L x [LN1, TMix (:618-649), residual, LN2, CMix (:673-679), residual], last-token select, ln_out, head,
+ * state[2] += T — launched as one sequence of sm_100a kernels on `stream`.
+ *
+ * Weights stay owned by the caller (device memory); the model object only records pointers.  Layouts are those of the
+ * reference's transformed `z` dict (Albatross/rwkv7.py:211-221) except ffn.value.weight, kept in checkpoint layout (C, 4C)
+ * = (N, K) so that every dense weight is K-major.
+ *   global_w[4]                : emb.weight (V,C) [ln0 already folded in, rwkv7.py:206], ln_out.weight, ln_out.bias, head.weight (V,C)
+ *   layer_w[n_layer * B200_LW_COUNT] : per layer, indexed by the B200_LW_* enum below
+ */
+enum {
+    B200_LW_LN1_W = 0, B200_LW_LN1_B, B200_LW_LN2_W, B200_LW_LN2_B,
+    B200_LW_X_R, B200_LW_X_W, B200_LW_X_K, B200_LW_X_V, B200_LW_X_A, B200_LW_X_G,
+    B200_LW_W0, B200_LW_W1 /* (D_w,C) */, B200_LW_W2 /* (C,D_w) */,
+    B200_LW_A0, B200_LW_A1, B200_LW_A2,
+    B200_LW_V0, B200_LW_V1, B200_LW_V2,      /* ignored on layer 0 (rwkv7.py:636) */
+    B200_LW_G1, B200_LW_G2,
+    B200_LW_K_K, B200_LW_K_A, B200_LW_R_K,
+    B200_LW_RECEPTANCE, B200_LW_KEY, B200_LW_VALUE, B200_LW_OUTPUT, /* (C,C) */
+    B200_LW_LNX_W, B200_LW_LNX_B,
+    B200_LW_FFN_X_K, B200_LW_FFN_KEY /* (4C,C) */, B200_LW_FFN_VALUE /* (C,4C) */,
+    B200_LW_COUNT
+};
+
+typedef struct b200_model b200_model;
+
+int b200_model_create(int n_layer, int n_embd, int vocab_size, int d_w, int d_a, int d_v, int d_g,
+                      const void* const* global_w, const void* const* layer_w, b200_model** out);
+void b200_model_destroy(b200_model* m);
+/* Scratch needed by b200_model_forward for up to max_tokens = B*T tokens per call (includes the linear workspace). */
+long b200_model_workspace_bytes(const b200_model* m, int max_tokens);
+
+/*
+ * One forward over B sequences x T tokens (decode: T = 1).  State tensors are the caller's, updated in place, and may be
+ * B-axis views of larger allocations (chirrup/worker.py:697-701), hence the explicit strides (in elements):
+ *   tokens      int32 (B*T) device, row-major (B,T)
+ *   state0      fp16 shift states; row of (layer l, which w in {0: TMix, 1: CMix}, slot s) at
+ *               state0 + l*s0_layer_stride + w*s0_which_stride + s*C          [reference shape (L,2,B,C), rwkv7.py:228]
+ *   state1      fp16 WKV states; tile (l, s, h) at state1 + l*s1_layer_stride + s*C*64 + h*4096   [(L,B,H,64,64), rwkv7.py:229]
+ *   elapsed     int32 (B) = state[2]; read by every layer, then += T (rwkv7.py:552)
+ *   slot_idx    int32 (B) or NULL; sequence b lives in slot slot_idx[b] of state0/state1 (elapsed stays indexed by b)
+ *   logits      fp16 (B, V), or (B*T, V) when full_output != 0; NULL skips ln_out + head (prefill that discards logits,
+ *               chirrup/worker.py:776)
+ *   workspace   b200_model_workspace_bytes(m, >= B*T) bytes, zero-initialised once by the caller
+ */
+int b200_model_forward(b200_model* m, int B, int T, const int* tokens, void* state0, long s0_layer_stride,
+                       long s0_which_stride, void* state1, long s1_layer_stride, int n_slots, int* elapsed,
+                       const int* slot_idx, void* logits, int full_output, void* workspace, long workspace_bytes,
+                       void* stream);
+/* Number of kernels the last b200_model_forward on this model launched (bench.py reports it as gpu_launches). */
+int b200_model_last_launch_count(const b200_model* m);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,7 +5,7 @@ import os
 import pytest
 import torch
 
-from tests.wkv_inputs import make_wkv_inputs
+from wkv_inputs import make_wkv_inputs
 
 pytestmark = pytest.mark.gpu
 
