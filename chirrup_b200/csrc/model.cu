@@ -1,6 +1,8 @@
 // The batched RWKV-7 step as one sequence of sm_100a kernel launches on a caller-supplied stream.
 // Follows RWKV_x070.forward_seq_batch_seperate (/root/reference/Albatross/rwkv7.py:555-563 -> _pre :503-509,
 // _layers :511-538, _post :540-553) with TMix = rwkv7.py:618-649 and CMix = :673-679.
+#include <cstdio>
+#include <cstdlib>
 #include <new>
 
 #include "common.cuh"
@@ -101,11 +103,16 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
     if (!workspace || workspace_bytes < ws.total) return B200_ERR_WORKSPACE;
     if (!slot_idx) n_slots = B;
     int n = 0, rc = 0;
-#define RUN(call)            \
-    do {                     \
-        rc = (call);         \
-        n++;                 \
-        if (rc) return rc;   \
+    static const bool debug_sync = getenv("B200_DEBUG_SYNC") != nullptr;
+#define RUN(call)                                                                                     \
+    do {                                                                                              \
+        rc = (call);                                                                                  \
+        n++;                                                                                          \
+        if (!rc && debug_sync) rc = (int)cudaStreamSynchronize(st);                                   \
+        if (rc) {                                                                                     \
+            if (debug_sync) fprintf(stderr, "[b200] launch #%d failed rc=%d: %s\n", n, rc, #call);    \
+            return rc;                                                                                \
+        }                                                                                             \
     } while (0)
     auto lin = [&](long rows, int N, int K, const __half* A, const __half* W, __half* out, const __half* bias,
                    const __half* res, int epi) {

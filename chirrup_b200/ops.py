@@ -34,6 +34,8 @@ def wkv7_forward_seq(state: torch.Tensor, r, w, k, v, a, b, elapsed_t: torch.Ten
     for n, t in (("state", state), ("r", r), ("w", w), ("k", k), ("v", v), ("a", a), ("b", b)):
         _req(t, n)
     _req(elapsed_t, "elapsed_t", torch.int32)
+    if B == 0 or T == 0:
+        return y if y is not None else torch.empty((B, T, C), dtype=torch.float16, device=r.device)
     if state.dim() != 4 or tuple(state.shape[1:]) != (H, HEAD, HEAD) or not state[0].is_contiguous():
         raise ValueError(f"state must be (n_slots,{H},64,64) with contiguous slots, got {tuple(state.shape)}")
     ins = [t if t.is_contiguous() else t.contiguous() for t in (r, w, k, v, a, b)]

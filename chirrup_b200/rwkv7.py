@@ -81,6 +81,7 @@ class RWKV_x070:
             rc = L.b200_layer_norm_f16(emb.shape[0], C, emb.data_ptr(), w["blocks.0.ln0.weight"].data_ptr(),
                                        w["blocks.0.ln0.bias"].data_ptr(), emb.data_ptr(), _stream(dev))
             _lib.check(rc, "b200_layer_norm_f16")
+        dims = {n: w[f"blocks.0.att.{n}1"].shape[0] for n in ("w", "a", "v", "g")}   # LoRA ranks, before the aliasing below
         for s in ("0", "1", "2"):                                             # rwkv7.py:207-209
             w[f"blocks.0.att.v{s}"] = w[f"blocks.0.att.a{s}"]
         self._w = w
@@ -91,7 +92,7 @@ class RWKV_x070:
         self._keep = g + lw
         GP = (ctypes.c_void_p * 4)(*[t.data_ptr() for t in g])
         LP = (ctypes.c_void_p * len(lw))(*[t.data_ptr() for t in lw])
-        d = lambda n: w[f"blocks.0.att.{n}1"].shape[0]
+        d = lambda n: dims[n]
         h = ctypes.c_void_p()
         rc = L.b200_model_create(self.n_layer, C, self.vocab_size, d("w"), d("a"), d("v"), d("g"), GP, LP, ctypes.byref(h))
         _lib.check(rc, "b200_model_create")

@@ -137,9 +137,16 @@ def run_one_case(name, geom_name, seed, n_steps):
 
 if __name__ == "__main__":
     torch.manual_seed(0)
+    only = set(sys.argv[1:])
+    _run_case, _run_one_case = run_case, run_one_case
+    run_case = lambda name, *a, **k: _run_case(name, *a, **k) if (not only or name in only) else None
+    run_one_case = lambda name, *a, **k: _run_one_case(name, *a, **k) if (not only or name in only) else None
     run_case("tiny_b3_p5_d4", "tiny", seed=0, B=3, prompt_len=5, n_decode=4)
     run_case("tiny_b2_p1_d6_wrap", "tiny", seed=1, B=2, prompt_len=1, n_decode=6, big_state_offset=(1 << 20) + 3)
     run_case("small_b4_p16_d8", "small", seed=2, B=4, prompt_len=16, n_decode=8)
     run_case("small_margin_b2_p4_d32", "small", seed=3, B=2, prompt_len=4, n_decode=32, recipe="margin")
     run_case("g01B_b1_p16_d8", "0.1B", seed=0, B=1, prompt_len=16, n_decode=8, store_state=False)
     run_one_case("tiny_one_s6", "tiny", seed=4, n_steps=6)
+    # the parity bar's recipe (chirrup_b200/synth.py "trained_like"): greedy tokens must be reproduced exactly
+    run_case("small_tl_b4_p8_d32", "small", seed=5, B=4, prompt_len=8, n_decode=32, recipe="trained_like")
+    run_case("g01B_tl_b2_p8_d8", "0.1B", seed=6, B=2, prompt_len=8, n_decode=8, recipe="trained_like", store_state=False)

@@ -23,7 +23,7 @@ def load_case(name):
     return np.load(os.path.join(GOLD, name + ".npz"))
 
 
-BATCH_CASES = ["tiny_b3_p5_d4", "tiny_b2_p1_d6_wrap", "small_b4_p16_d8", "small_margin_b2_p4_d32"]
+BATCH_CASES = ["tiny_b3_p5_d4", "tiny_b2_p1_d6_wrap", "small_b4_p16_d8", "small_margin_b2_p4_d32", "small_tl_b4_p8_d32"]
 
 
 @pytest.mark.parametrize("name", BATCH_CASES)
