@@ -1,0 +1,364 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: RWKV-7 batched decode step (BASELINE.json metric
+"RWKV-7 7.2B decode tok/s/GPU @bsz256; WKV step HBM GB/s vs peak").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--geom 7.2B] [--bsz 256]
+
+One "step" = one decode forward (T = 1) of `bsz` sequences per GPU through every layer + head + greedy sampling.
+N > 1: launched by torchrun, one replica per GPU, requests sharded by rank, no data-path collective ("weak" scaling); NCCL is
+used only for the barrier and the max-over-ranks of the device time.
+
+Printed JSON keys (contract in the task statement): value = whole-job tok/s with inputs resident in HBM (CUDA-graph replay of
+the step, CUDA events); e2e = the same through the public Python API with HOST token buffers (pinned H2D of token ids, D2H
+of the sampled ids, every step); roofline = the WKV kernel against measured HBM peak; cpu_baseline = the CPU oracle
+(the reference's PyTorch CPU path, oracle/rwkv7_oracle.py) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch
+
+METRIC = "RWKV-7 7.2B decode tok/s/GPU @bsz256; WKV step HBM GB/s vs peak"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--geom", default="7.2B")
+    ap.add_argument("--bsz", type=int, default=256)
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-layers", type=int, default=2, help="layers of the geometry the CPU sample runs")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured"
+    except Exception:
+        return 6650.0, 1400.0, "fallback"
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._t is not None:
+            self._t.join()
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ----------------------------------------------------------------------------------------------- CPU baseline / reference arm
+def cpu_reference_sample(geom_name: str, bsz: int, n_layers: int, steps: int, warmup: int = 1):
+    """Times the reference's PyTorch CPU path (the oracle: same ATen fp16 ops in the same order as Albatross/rwkv7.py, WKV body
+    from oracle/wkv7_oracle.c) on a bounded sample of the workload: one decode step of `bsz` sequences through the first
+    `n_layers` layers + ln_out + head of the geometry; the full-depth step time is body/n_layers * L + head.
+    Returns (tok/s extrapolated to the full depth, description, cores, per-step seconds list)."""
+    from chirrup_b200.synth import GEOMETRIES, make_checkpoint
+    from oracle import rwkv7_oracle as O
+
+    geom = GEOMETRIES[geom_name]
+    n_layers = min(n_layers, geom.n_layer)
+    raw = make_checkpoint(geom, seed=0, recipe="trained_like", n_layer=n_layers)
+    z = O.transform_checkpoint(raw)
+    del raw
+    og = O.Geometry(z)
+    st = O.zero_state(og, bsz)
+    g = torch.Generator().manual_seed(0)
+    toks = torch.randint(1, geom.vocab_size, (bsz, 1), generator=g).tolist()
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        O.forward_seq_batch(z, og, toks, st, skip_head=True)
+        t1 = time.perf_counter()
+        O.forward_seq_batch(z, og, toks, st, layer_range=(0, 0))   # embedding + ln_out + head only
+        t2 = time.perf_counter()
+        if i >= warmup:
+            times.append(((t1 - t0) / n_layers * geom.n_layer + (t2 - t1)))
+    step_s = sum(times) / len(times)
+    cores = torch.get_num_threads()
+    sample = (f"oracle (reference PyTorch CPU path, fp16 ATen ops + C WKV) on {geom_name} geometry, bsz {bsz}, T=1: "
+              f"{steps} timed step(s) of {n_layers}/{geom.n_layer} layers + head, extrapolated to {geom.n_layer} layers; "
+              f"{cores} threads of {os.cpu_count()} cpus")
+    return bsz / step_s, sample, cores, times
+
+
+# ----------------------------------------------------------------------------------------------- our arm
+def build_model(geom_name: str, device):
+    from chirrup_b200.rwkv7 import RWKV_x070, make_args
+    from chirrup_b200.synth import GEOMETRIES, make_checkpoint
+
+    geom = GEOMETRIES[geom_name]
+    raw = make_checkpoint(geom, seed=0, recipe="trained_like", device=device, dtype=torch.float16)
+    m = RWKV_x070(make_args(), state_dict=raw, device=device)
+    del raw
+    torch.cuda.empty_cache()
+    return geom, m
+
+
+def time_wkv_kernel(m, geom, state, bsz, reps=5):
+    """Average device time of one WKV launch (T = 1) over the model's real per-layer state (L x bsz x 16 MiB-per-7.2B-slot >> L2),
+    CUDA events on the launching (current) stream."""
+    from chirrup_b200 import ops
+
+    C, H, L = geom.n_embd, geom.n_head, geom.n_layer
+    dev = state[1].device
+    mk = lambda s: (torch.randn(bsz, 1, C, device=dev) * s).half()
+    r, k, v = mk(0.5), mk(0.5), mk(0.5)
+    w = (torch.randn(bsz, 1, C, device=dev) - 1).half()
+    kk = torch.nn.functional.normalize(torch.randn(bsz, 1, H, 64, device=dev), dim=-1).view(bsz, 1, C)
+    a, b = (-kk).half(), (kk * torch.sigmoid(torch.randn(bsz, 1, C, device=dev))).half()
+    y = torch.empty_like(r)
+    et = torch.zeros(bsz, dtype=torch.int32, device=dev)
+    scratch = state[1].clone()
+    run = lambda: [ops.wkv7_forward_seq(scratch[l], r, w, k, v, a, b, et, y=y) for l in range(L)]
+    run()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g = torch.cuda.CUDAGraph()   # replay so that host launch overhead does not pollute the per-launch device time
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        run()
+        with torch.cuda.graph(g, stream=s):
+            run()
+    torch.cuda.current_stream().wait_stream(s)
+    g.replay()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    del scratch
+    return e0.elapsed_time(e1) * 1e-3 / (reps * L)
+
+
+def run_ours(a, rank, world, device):
+    from chirrup_b200 import _lib, ops
+
+    geom, m = build_model(a.geom, device)
+    B, V = a.bsz, geom.vocab_size
+    state = m.generate_zero_state(B)
+    gen = torch.Generator().manual_seed(1234 + rank)
+    prompt = torch.randint(1, V, (B, 16), generator=gen)
+    m.forward_seq_batch(prompt.tolist(), state)          # short synthetic prompt so the state is not all zeros
+    tok = torch.randint(1, V, (B,), generator=gen).to(torch.int32).to(device)
+    logits = torch.empty((B, V), dtype=torch.float16, device=device)
+    nxt = torch.empty((B,), dtype=torch.int32, device=device)
+
+    def step():   # one decode step, everything resident in HBM: forward -> logits -> greedy sample -> next token ids
+        m._step(tok, B, 1, state, False, out=logits)
+        ops.argmax(logits, out=nxt)
+        tok.copy_(nxt)
+
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    launches_per_step = _lib.lib().b200_model_last_launch_count(m._handle) + 1   # + argmax (the token copy is a memcpy node)
+    graph = None
+    if not a.no_graph:
+        try:
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                step()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=s):
+                    step()
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+        except Exception as e:  # noqa: BLE001 — report and time eager launches instead
+            sys.stderr.write(f"[bench] CUDA graph capture failed ({e!r}); timing eager launches\n")
+            graph = None
+    do_step = graph.replay if graph is not None else step
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(a.warmup):
+        do_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(device.index or 0) as clk:
+        e0.record()
+        for _ in range(a.steps):
+            do_step()
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    barrier()
+
+    # ---- end to end through the public API with host buffers (the call Chirrup's worker makes, chirrup/worker.py:704)
+    host_tok = torch.randint(1, V, (B, 1), generator=gen).to(torch.int32).pin_memory()
+    host_out = torch.empty((B,), dtype=torch.int32).pin_memory()
+
+    def e2e_step():
+        # public API, host token ids in (pinned (B,1) int32): H2D copy + RWKV_x070.forward_seq_batch_seperate (C ABI)
+        lg = m.forward_seq_batch_seperate(host_tok, state)
+        ops.argmax(lg, out=nxt)
+        host_out.copy_(nxt, non_blocking=True)                                  # D2H of the sampled ids
+        torch.cuda.current_stream().synchronize()
+        host_tok.view(-1).copy_(host_out)                                       # next step's input comes from the host side
+
+    for _ in range(max(3, a.warmup)):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+
+    wkv_s = time_wkv_kernel(m, geom, state, B) if rank == 0 else 0.0
+    times = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=device)
+    if world > 1:
+        torch.distributed.all_reduce(times, op=torch.distributed.ReduceOp.MAX)
+    ms, e2e_ms = times.tolist()
+    return dict(geom=geom, ms=ms, e2e_ms=e2e_ms, clocks=clk.summary(), launches=launches_per_step * a.steps,
+                graph=graph is not None, wkv_s=wkv_s, B=B)
+
+
+# ----------------------------------------------------------------------------------------------- main
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    from chirrup_b200.synth import GEOMETRIES
+
+    geom = GEOMETRIES[a.geom]
+    config = {"workload": f"RWKV-7 g1 {a.geom} (L{geom.n_layer}, D{geom.n_embd}) fp16 decode, bsz {a.bsz}/GPU, T=1, "
+                          f"greedy sampling, one replica per GPU (BASELINE.json configs[2])",
+              "batch_per_gpu": a.bsz, "weights": "random-init trained_like recipe (chirrup_b200/synth.py), seed 0",
+              "l2": "weights (14.4 GB at 7.2B) + state (4.3 GB) streamed every step: inputs larger than L2, no flush needed",
+              "parallelism": f"replicas x{max(world, 1)} (requests sharded by rank, no collective on the step path)"}
+    base = {"metric": METRIC, "unit": "tok/s", "n_gpus": max(world, 1), "steps": a.steps, "warmup": a.warmup,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+            "config": config}
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        # The reference's own CPU implementation of the path: its PyTorch model code on the host cores (the oracle restates it op for
+        # op and is pinned bit-identical to it on CPU; the reference cannot be imported on the GPU box, /root/reference is absent).
+        v, sample, cores, times = cpu_reference_sample(a.geom, a.bsz, a.cpu_layers, max(1, min(a.steps, 3)), warmup=1)
+        out = dict(base)
+        out.update({"impl": "reference", "value": v, "ms_per_step": 1e3 * a.bsz / v, "n_gpus": max(world, 1),
+                    "cpu_baseline": {"value": v, "unit": "tok/s", "cores": cores, "kind": "port", "sample": sample},
+                    "e2e": {"value": v, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                    "gpu_launches": 0})
+        print(json.dumps(out))
+        return
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl ours needs a CUDA device: chirrup_b200 has no CPU path")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.distributed.init_process_group("nccl", device_id=device)
+    r = run_ours(a, rank, world, device)
+    if rank == 0:
+        hbm_peak, tf_peak, which = peaks()
+        n = max(world, 1)
+        value = n * a.bsz * a.steps / (r["ms"] * 1e-3)
+        e2e = n * a.bsz * a.steps / (r["e2e_ms"] * 1e-3)
+        g = r["geom"]
+        wkv_bytes = a.bsz * (2 * g.n_head * 64 * 64 * 2 + 7 * g.n_embd * 2 + 4)     # SURVEY.md §8(d), per launch (one layer)
+        achieved = wkv_bytes / r["wkv_s"] / 1e9
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "wkv_traffic.json"))).get(f"{a.geom}_bsz{a.bsz}")
+        except Exception:
+            pass
+        out = dict(base)
+        out.update({
+            "value": value, "ms_per_step": r["ms"] / a.steps,
+            "e2e": {"value": e2e, "unit": "tok/s", "h2d_bytes_per_step": a.bsz * 4, "d2h_bytes_per_step": a.bsz * 4,
+                    "api": "RWKV_x070.forward_seq_batch_seperate(host token ids) + greedy sample + D2H of the ids"},
+            "gpu_launches": r["launches"], "cuda_graph": r["graph"], "clocks": r["clocks"],
+            "roofline": {"bound": "hbm", "kernel": "wkv7_seq_kernel (T=1)", "achieved": achieved, "peak": hbm_peak,
+                         "unit": "GB/s", "frac": achieved / hbm_peak, "frac_of_8TBps_nominal": achieved / 8000.0,
+                         "traffic": traffic, "peak_source": which, "algorithmic_bytes_per_launch": wkv_bytes,
+                         "us_per_launch": r["wkv_s"] * 1e6,
+                         "wkv_share_of_step": r["wkv_s"] * g.n_layer / (r["ms"] * 1e-3 / a.steps)},
+            "gemm": {"flops_per_step": g.gemm_flops_per_token() * a.bsz,
+                     "achieved_tflops_if_rest_of_step": g.gemm_flops_per_token() * a.bsz / max(1e-9, (r["ms"] * 1e-3 / a.steps - r["wkv_s"] * g.n_layer)) / 1e12,
+                     "peak_tflops": tf_peak},
+        })
+        if not a.skip_cpu_baseline and world == 1:
+            v, sample, cores, _ = cpu_reference_sample(a.geom, a.bsz, a.cpu_layers, 1, warmup=1)
+            out["cpu_baseline"] = {"value": v, "unit": "tok/s", "cores": cores, "kind": "port", "sample": sample}
+        print(json.dumps(out))
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -204,6 +204,39 @@ __global__ void __launch_bounds__(128) tmix_post_kernel(TmixPostArgs p) {
     st2(p.out + i, hr(o0 * g.x), hr(o1 * g.y));
 }
 
+// Greedy sampling: out[b] = first index of the maximum of logits[b, :] compared as fp32 (== torch.argmax(logits.float(), -1),
+// the worker's top_k == 1 / temperature == 0 path, chirrup/utils/samplers.py:171-255).  One CTA per row.
+__global__ void __launch_bounds__(256) argmax_rows_kernel(int V, const __half* __restrict__ logits, long ld,
+                                                          int* __restrict__ out) {
+    __shared__ float sv[8];
+    __shared__ int si[8];
+    const __half* row = logits + (size_t)blockIdx.x * ld;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int c = threadIdx.x * 8; c < V; c += 256 * 8) {
+        int4 q = *reinterpret_cast<const int4*>(row + c);
+        const __half* h = reinterpret_cast<const __half*>(&q);
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            const float v = __half2float(h[e]);
+            if (v > best || (v == best && c + e < bi)) best = v, bi = c + e;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) best = ov, bi = oi;
+    }
+    if ((threadIdx.x & 31) == 0) sv[threadIdx.x >> 5] = best, si[threadIdx.x >> 5] = bi;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; w++)
+            if (sv[w] > best || (sv[w] == best && si[w] < bi)) best = sv[w], bi = si[w];
+        out[blockIdx.x] = bi;
+    }
+}
+
 int ln_threads(int C) {
     int t = (C / 8 + 31) / 32 * 32;
     return t < 32 ? 32 : t;
@@ -237,6 +270,11 @@ int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off
 int launch_add_elapsed(int B, int T, int* elapsed, cudaStream_t s) {
     if (B <= 0) return 0;
     add_elapsed_kernel<<<(B + 127) / 128, 128, 0, s>>>(B, T, elapsed);
+    return (int)cudaGetLastError();
+}
+int launch_argmax_rows(int rows, int V, const __half* logits, long ld, int* out, cudaStream_t s) {
+    if (rows <= 0) return 0;
+    argmax_rows_kernel<<<rows, 256, 0, s>>>(V, logits, ld, out);
     return (int)cudaGetLastError();
 }
 int launch_tmix_prep(const TmixPrepArgs& a, cudaStream_t s) {

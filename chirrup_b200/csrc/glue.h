@@ -20,6 +20,7 @@ int launch_ln_shift_mix1(int B, int T, int C, const __half* x, const __half* ln_
 int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off, const __half* ln_w, const __half* ln_b,
                    __half* out, cudaStream_t s);
 int launch_add_elapsed(int B, int T, int* elapsed, cudaStream_t s);
+int launch_argmax_rows(int rows, int V, const __half* logits, long ld, int* out, cudaStream_t s);
 
 struct TmixPrepArgs {
     int M, C;

@@ -193,3 +193,8 @@ extern "C" int b200_layer_norm_f16(int rows, int C, const void* x, const void* w
     return launch_ln_rows(rows, C, static_cast<const __half*>(x), 1, 0, static_cast<const __half*>(w),
                           static_cast<const __half*>(b), static_cast<__half*>(out), static_cast<cudaStream_t>(stream));
 }
+
+extern "C" int b200_argmax_f16(int rows, int V, const void* logits, long ld, int* out, void* stream) {
+    if (rows < 0 || V <= 0 || (V & 7) || (ld & 7)) return B200_ERR_BAD_ARG;
+    return launch_argmax_rows(rows, V, static_cast<const __half*>(logits), ld, out, static_cast<cudaStream_t>(stream));
+}

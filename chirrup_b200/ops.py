@@ -116,3 +116,14 @@ def linear(x: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor] = None
                                     ws.numel(), _stream(x))
     _lib.check(rc, "b200_linear_f16")
     return out.view(*x.shape[:-1], N)
+
+
+def argmax(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Greedy sampling: (B, V) fp16 logits -> (B,) int32 token ids (lowest index on ties, like ``torch.argmax`` on fp32)."""
+    _req(logits, "logits")
+    B, V = logits.shape
+    if out is None:
+        out = torch.empty((B,), dtype=torch.int32, device=logits.device)
+    rc = _lib.lib().b200_argmax_f16(B, V, logits.data_ptr(), logits.stride(0), out.data_ptr(), _stream(logits))
+    _lib.check(rc, "b200_argmax_f16")
+    return out

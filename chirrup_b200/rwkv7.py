@@ -165,7 +165,7 @@ class RWKV_x070:
 
     def _tokens(self, idxs) -> torch.Tensor:
         if torch.is_tensor(idxs):
-            return idxs.to(device=self.device, dtype=torch.int32).reshape(-1).contiguous()
+            return idxs.to(device=self.device, dtype=torch.int32, non_blocking=True).reshape(-1).contiguous()
         return torch.tensor(idxs, dtype=torch.int32).reshape(-1).to(self.device, non_blocking=True)
 
     def forward_seq_batch(self, idxs: Sequence[Sequence[int]], state: List[torch.Tensor], full_output: bool = False):

@@ -133,6 +133,10 @@ int b200_model_forward(b200_model* m, int B, int T, const int* tokens, void* sta
                        long s0_which_stride, void* state1, long s1_layer_stride, int n_slots, int* elapsed,
                        const int* slot_idx, void* logits, int full_output, void* workspace, long workspace_bytes,
                        void* stream);
+/* Greedy sampling of `rows` logit rows (fp16, V columns, row pitch ld): out[i] = lowest index of the row maximum (int32).
+ * The top_k == 1 case of the worker's sampler (chirrup/worker.py:733-740, chirrup/utils/samplers.py:171-255). */
+int b200_argmax_f16(int rows, int V, const void* logits, long ld, int* out, void* stream);
+
 /* Number of kernels the last b200_model_forward on this model launched (bench.py reports it as gpu_launches). */
 int b200_model_last_launch_count(const b200_model* m);
 
