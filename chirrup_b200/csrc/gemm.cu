@@ -23,7 +23,9 @@ namespace {
 constexpr int BK = 64;
 constexpr int GEMM_THREADS = 192;
 constexpr int MAX_SPLIT = 8;                      // portable cluster size
-constexpr long WS_BYTES = 160L * 256 * 256 * 4;  // partial-tile capacity: > 148 CTAs x the largest (256 x 256 fp32) tile
+constexpr int STG_LD = 36;  // row pitch (floats) of staged / parked 32-column units: 16-byte aligned rows, conflict-free 128-bit accesses
+constexpr int UNIT_FLOATS = 128 * STG_LD;         // one parked unit: 128 rows x 32 columns (+4 pad) fp32 = 18 KiB
+constexpr long WS_BYTES = 160L * 64 * UNIT_FLOATS * 4;  // > 148 CTAs x the largest tile (256 x 256 = 64 units)
 
 template <int MT, int BN>
 struct Cfg {
@@ -51,45 +53,39 @@ DEVI float epilogue_op(float acc, float bias, float res) {
     return res + round_h(acc);  // B200_EPI_RESADD
 }
 
-// 32 consecutive output columns of one row: acc[] fp32 -> fp16 global, 16-byte stores.
+// Four consecutive output columns of one row: fp32 -> epilogue -> fp16, one 8-byte store.  In the epilogue's coalesced
+// layout a warp instruction covers 4 rows x 64 contiguous bytes.
 template <int EPI>
-DEVI void store_row32(const float (&acc)[32], __half* __restrict__ out_row, const __half* __restrict__ bias,
-                      const __half* __restrict__ res_row, int col0, int N) {
+DEVI void finish4(const float4 acc, __half* __restrict__ out_row, const __half* __restrict__ bias,
+                  const __half* __restrict__ res_row, int c) {
+    float a[4] = {acc.x, acc.y, acc.z, acc.w};
+    float bv[4] = {0.f, 0.f, 0.f, 0.f}, rv[4] = {0.f, 0.f, 0.f, 0.f};
+    if ((EPI == B200_EPI_NONE || EPI == B200_EPI_TANH || EPI == B200_EPI_SIGMOID) && bias != nullptr) {
+        uint2 q = *reinterpret_cast<const uint2*>(bias + c);
+        const __half* p = reinterpret_cast<const __half*>(&q);
 #pragma unroll
-    for (int g = 0; g < 4; g++) {
-        const int c = col0 + g * 8;
-        if (c >= N) break;
-        float bv[8], rv[8];
-#pragma unroll
-        for (int e = 0; e < 8; e++) bv[e] = 0.f, rv[e] = 0.f;
-        if ((EPI == B200_EPI_NONE || EPI == B200_EPI_TANH || EPI == B200_EPI_SIGMOID) && bias != nullptr) {
-            int4 q = *reinterpret_cast<const int4*>(bias + c);
-            const __half* p = reinterpret_cast<const __half*>(&q);
-#pragma unroll
-            for (int e = 0; e < 8; e++) bv[e] = __half2float(p[e]);
-        }
-        if (EPI == B200_EPI_RESADD) {
-            int4 q = *reinterpret_cast<const int4*>(res_row + c);
-            const __half* p = reinterpret_cast<const __half*>(&q);
-#pragma unroll
-            for (int e = 0; e < 8; e++) rv[e] = __half2float(p[e]);
-        }
-        int4 o;
-        __half* po = reinterpret_cast<__half*>(&o);
-#pragma unroll
-        for (int e = 0; e < 8; e++) po[e] = __float2half_rn(epilogue_op<EPI>(acc[g * 8 + e], bv[e], rv[e]));
-        *reinterpret_cast<int4*>(out_row + c) = o;
+        for (int e = 0; e < 4; e++) bv[e] = __half2float(p[e]);
     }
+    if (EPI == B200_EPI_RESADD) {
+        uint2 q = *reinterpret_cast<const uint2*>(res_row + c);
+        const __half* p = reinterpret_cast<const __half*>(&q);
+#pragma unroll
+        for (int e = 0; e < 4; e++) rv[e] = __half2float(p[e]);
+    }
+    uint2 o;
+    __half* po = reinterpret_cast<__half*>(&o);
+#pragma unroll
+    for (int e = 0; e < 4; e++) po[e] = __float2half_rn(epilogue_op<EPI>(a[e], bv[e], rv[e]));
+    *reinterpret_cast<uint2*>(out_row + c) = o;
 }
 
-DEVI void store_row32_rt(int epi, const float (&acc)[32], __half* out_row, const __half* bias, const __half* res_row,
-                         int col0, int N) {
+DEVI void finish4_rt(int epi, const float4 acc, __half* out_row, const __half* bias, const __half* res_row, int c) {
     switch (epi) {
-        case B200_EPI_NONE: store_row32<B200_EPI_NONE>(acc, out_row, bias, res_row, col0, N); break;
-        case B200_EPI_TANH: store_row32<B200_EPI_TANH>(acc, out_row, bias, res_row, col0, N); break;
-        case B200_EPI_SIGMOID: store_row32<B200_EPI_SIGMOID>(acc, out_row, bias, res_row, col0, N); break;
-        case B200_EPI_RELU_SQ: store_row32<B200_EPI_RELU_SQ>(acc, out_row, bias, res_row, col0, N); break;
-        default: store_row32<B200_EPI_RESADD>(acc, out_row, bias, res_row, col0, N); break;
+        case B200_EPI_NONE: finish4<B200_EPI_NONE>(acc, out_row, bias, res_row, c); break;
+        case B200_EPI_TANH: finish4<B200_EPI_TANH>(acc, out_row, bias, res_row, c); break;
+        case B200_EPI_SIGMOID: finish4<B200_EPI_SIGMOID>(acc, out_row, bias, res_row, c); break;
+        case B200_EPI_RELU_SQ: finish4<B200_EPI_RELU_SQ>(acc, out_row, bias, res_row, c); break;
+        default: finish4<B200_EPI_RESADD>(acc, out_row, bias, res_row, c); break;
     }
 }
 
@@ -103,7 +99,26 @@ struct GemmArgs {
     float* partials;  // [tile][split][unit][128][32] fp32
     int kb_per_split;
     int n_split;      // == cluster size along z
+    unsigned long long* dbg;  // optional timeline probe (globaltimer ns), 8 slots per CTA; nullptr in production
 };
+
+DEVI unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define PROBE(slot)                                                                                         \
+    do {                                                                                                    \
+        if (g.dbg && (threadIdx.x == 64 || ((slot) == 2 && threadIdx.x == 32)))                             \
+            g.dbg[((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + (slot)] = gtime(); \
+    } while (0)
+
+// shared -> global linear bulk copy (TMA engine), tracked by the issuing thread's bulk async-group
+DEVI void bulk_store(void* gdst, const void* ssrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(reinterpret_cast<uint64_t>(gdst)),
+                 "r"(smem_u32(ssrc)), "r"(bytes)
+                 : "memory");
+}
 
 DEVI void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
@@ -131,6 +146,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     const int kb1 = min(kb_total, kb0 + g.kb_per_split);
     const int n_kb = kb1 - kb0;  // >= 1 by construction of the launch
     const bool splitk = g.n_split > 1;
+    PROBE(0);
 
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tmA);
@@ -147,10 +163,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    PROBE(1);
 
     const int q = warp & 3;  // TMEM lane quarter of an epilogue warp
     const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
-    const int lrow = q * 32 + lane;
 
     if (warp == 0) {
         if (lane == 0) {
@@ -177,6 +193,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 const int s = it % C::kStages;
                 const uint32_t ph = (it / C::kStages) & 1;
                 mbar_wait(&full_bar[s], ph);
+                if (it == 0) PROBE(2);
                 tc_fence_after();
                 const uint32_t st = smem_u32(smem + s * C::kStageBytes);
                 const uint64_t bdesc = umma_desc_sw128(st + C::kABytes);
@@ -195,68 +212,102 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         }
         __syncwarp();
     } else {
-        // ---- epilogue warps, phase 1: drain TMEM
+        // ---- epilogue warps, phase 1: drain TMEM.  tcgen05.ld gives thread = row; a per-warp shared-memory transpose (the
+        // pipeline stages are idle by now) turns that into lane = 4 consecutive columns so that every global access is coalesced.
         mbar_wait(accum_bar, 0);
+        PROBE(3);
         tc_fence_after();
-        float* my_part = splitk ? g.partials + ((size_t)tile_id * g.n_split + split) * (size_t)C::kUnits * 128 * 32 : nullptr;
+        // two staging buffers per warp in the (now idle) pipeline stages
+        float* stg0 = reinterpret_cast<float*>(smem) + q * (2 * 32 * STG_LD);
+        float* my_part = splitk ? g.partials + ((size_t)tile_id * g.n_split + split) * (size_t)C::kUnits * UNIT_FLOATS : nullptr;
+        const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;
+        int n_parked = 0;
 #pragma unroll 1
         for (int u = 0; u < C::kUnits; u++) {
             const int mt = u / (BN / 32), c = u - mt * (BN / 32);
             if (n0 + c * 32 >= g.N) continue;  // columns past N (N tail of the last tile)
+            float* stg = stg0 + (n_parked & 1) * (32 * STG_LD);
+            if (splitk && n_parked >= 2) {  // the bulk store that last used this buffer must have read it
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+            }
             uint32_t v[32];
             tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + mt * BN + c * 32, v);
             tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 8; e++)
+                *reinterpret_cast<float4*>(stg + lane * STG_LD + 4 * e) =
+                    make_float4(__uint_as_float(v[4 * e]), __uint_as_float(v[4 * e + 1]), __uint_as_float(v[4 * e + 2]),
+                                __uint_as_float(v[4 * e + 3]));
             if (splitk) {
-                float4* dst = reinterpret_cast<float4*>(my_part + ((size_t)u * 128 + lrow) * 32);
-#pragma unroll
-                for (int e = 0; e < 8; e++)
-                    __stcg(dst + e, make_float4(__uint_as_float(v[4 * e]), __uint_as_float(v[4 * e + 1]),
-                                                __uint_as_float(v[4 * e + 2]), __uint_as_float(v[4 * e + 3])));
-            } else {
-                const int row = m0 + mt * 128 + lrow;
-                if (row < g.M) {
-                    float acc[32];
-#pragma unroll
-                    for (int e = 0; e < 32; e++) acc[e] = __uint_as_float(v[e]);
-                    store_row32_rt(g.epi, acc, g.out + (size_t)row * g.ldo, g.bias,
-                                   g.residual ? g.residual + (size_t)row * g.ldo : nullptr, n0 + c * 32, g.N);
+                // park this warp's 32 rows of the unit (one contiguous 4.5 KiB slab) with a TMA bulk store
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    bulk_store(my_part + (size_t)u * UNIT_FLOATS + (size_t)q * 32 * STG_LD, stg, 32 * STG_LD * 4);
+                    tma_store_commit();
                 }
+                n_parked++;
+            } else {
+                __syncwarp();
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const int r = i * 4 + sub_r;  // row inside this warp's 32
+                    const float4 t = *reinterpret_cast<const float4*>(stg + r * STG_LD + sub_c);
+                    const int row = m0 + mt * 128 + q * 32 + r, col = n0 + c * 32 + sub_c;
+                    if (row < g.M && col < g.N)
+                        finish4_rt(g.epi, t, g.out + (size_t)row * g.ldo, g.bias,
+                                   g.residual ? g.residual + (size_t)row * g.ldo : nullptr, col);
+                }
+                __syncwarp();
             }
         }
+        if (splitk && lane == 0) {
+            tma_store_wait<0>();  // all parked slabs are written
+            asm volatile("fence.proxy.async;" ::: "memory");
+        }
+        __syncwarp();
     }
 
     if (splitk) {
         // every CTA of the cluster (= every K split of this tile) has parked its partial: release/acquire at cluster scope
+        PROBE(4);
         __threadfence();
         cluster_sync_all();
+        PROBE(5);
         if (warp >= 2) {
-            const float* base = g.partials + (size_t)tile_id * g.n_split * (size_t)C::kUnits * 128 * 32;
+            const float* base = g.partials + (size_t)tile_id * g.n_split * (size_t)C::kUnits * UNIT_FLOATS;
+            const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;
 #pragma unroll 1
             for (int u = split; u < C::kUnits; u += g.n_split) {  // this CTA's share of the tile
                 const int mt = u / (BN / 32), c = u - mt * (BN / 32);
-                const int row = m0 + mt * 128 + lrow;
-                if (n0 + c * 32 >= g.N || row >= g.M) continue;
-                float acc[32];
+                if (n0 + c * 32 >= g.N) continue;
+                float4 acc[8];
 #pragma unroll
-                for (int e = 0; e < 32; e++) acc[e] = 0.f;
-#pragma unroll 2
+                for (int i = 0; i < 8; i++) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
                 for (int z = 0; z < g.n_split; z++) {  // fixed order: deterministic sum
-                    const float4* src =
-                        reinterpret_cast<const float4*>(base + (((size_t)z * C::kUnits + u) * 128 + lrow) * 32);
+                    const float* src = base + ((size_t)z * C::kUnits + u) * UNIT_FLOATS + (size_t)(q * 32 + sub_r) * STG_LD + sub_c;
                     float4 t[8];
 #pragma unroll
-                    for (int e = 0; e < 8; e++) t[e] = __ldcg(src + e);
+                    for (int i = 0; i < 8; i++) t[i] = __ldcg(reinterpret_cast<const float4*>(src + (size_t)i * 4 * STG_LD));
 #pragma unroll
-                    for (int e = 0; e < 8; e++) {
-                        acc[4 * e] += t[e].x; acc[4 * e + 1] += t[e].y; acc[4 * e + 2] += t[e].z; acc[4 * e + 3] += t[e].w;
+                    for (int i = 0; i < 8; i++) {
+                        acc[i].x += t[i].x; acc[i].y += t[i].y; acc[i].z += t[i].z; acc[i].w += t[i].w;
                     }
                 }
-                store_row32_rt(g.epi, acc, g.out + (size_t)row * g.ldo, g.bias,
-                               g.residual ? g.residual + (size_t)row * g.ldo : nullptr, n0 + c * 32, g.N);
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const int row = m0 + mt * 128 + q * 32 + i * 4 + sub_r, col = n0 + c * 32 + sub_c;
+                    if (row < g.M && col < g.N)
+                        finish4_rt(g.epi, acc[i], g.out + (size_t)row * g.ldo, g.bias,
+                                   g.residual ? g.residual + (size_t)row * g.ldo : nullptr, col);
+                }
             }
         }
     }
 
+    PROBE(6);
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
@@ -268,24 +319,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 struct GemmPlan {
     int mt, bn, grid_x, grid_y, n_split, kb_per_split;
 };
-
-// Tile shape and K split for a problem.  Decode-sized problems get one wave of <= 148 CTAs.
-static GemmPlan plan_gemm(int M, int N, int K) {
-    GemmPlan p;
-    const int kb = (K + BK - 1) / BK;
-    p.mt = (M > 128) ? 2 : 1;
-    p.bn = (N >= 1024 && kb >= 16) ? 256 : 32;
-    p.grid_x = (N + p.bn - 1) / p.bn;
-    p.grid_y = (M + 128 * p.mt - 1) / (128 * p.mt);
-    const long tiles = (long)p.grid_x * p.grid_y;
-    int s = (int)(148 / tiles);
-    if (s > kb / 2) s = kb / 2;  // >= 2 K-blocks per split
-    if (s > MAX_SPLIT) s = MAX_SPLIT;
-    if (s < 1) s = 1;
-    p.kb_per_split = (kb + s - 1) / s;
-    p.n_split = (kb + p.kb_per_split - 1) / p.kb_per_split;  // no empty splits
-    return p;
-}
 
 template <int MT, int BN>
 static int launch_cfg(const GemmPlan& p, const CUtensorMap& tmA, const CUtensorMap& tmW, const GemmArgs& g, cudaStream_t stream) {
@@ -311,7 +344,79 @@ static int launch_cfg(const GemmPlan& p, const CUtensorMap& tmA, const CUtensorM
     return (int)cudaLaunchKernelEx(&cfg, gemm_kernel<MT, BN>, tmA, tmW, g);
 }
 
+// How many clusters of `s` CTAs of this configuration the device can hold at once (GPC boundaries strand SMs for big clusters).
+template <int MT, int BN>
+static int max_clusters_cfg(int s) {
+    using C = Cfg<MT, BN>;
+    static int cache[MAX_SPLIT + 1] = {0};
+    if (cache[s]) return cache[s];
+    cudaFuncSetAttribute(gemm_kernel<MT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(1, 1, s);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = C::kSmemBytes;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = s;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_kernel<MT, BN>, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = 148 / s - (s > 2 ? 2 : 0);  // conservative guess
+    }
+    cache[s] = n;
+    return n;
+}
+
+static int max_clusters(int mt, int bn, int s) {
+    if (mt == 2) return bn == 256 ? max_clusters_cfg<2, 256>(s) : bn == 128 ? max_clusters_cfg<2, 128>(s) : max_clusters_cfg<2, 32>(s);
+    return bn == 256 ? max_clusters_cfg<1, 256>(s) : bn == 128 ? max_clusters_cfg<1, 128>(s) : max_clusters_cfg<1, 32>(s);
+}
+
+// Tile shape and K split.  Candidates (BN, S) are ranked by a small cost model of one CTA's life (measured rates):
+// operand bytes through its shared memory, fp32 partial bytes parked + re-read when S > 1, and the number of waves.
+static GemmPlan plan_gemm(int M, int N, int K) {
+    const int kb = (K + BK - 1) / BK;
+    const int mt = (M > 128) ? 2 : 1;
+    const int gy = (M + 128 * mt - 1) / (128 * mt);
+    GemmPlan best = {};
+    double best_cost = 1e30;
+    const int bns[3] = {256, 128, 32};
+    for (int bi = 0; bi < 3; bi++) {
+        const int bn = bns[bi];
+        if (bn > 32 && N < 2 * bn) continue;  // skinny outputs: small tiles
+        const int gx = (N + bn - 1) / bn;
+        const long tiles = (long)gx * gy;
+        for (int s = 1; s <= MAX_SPLIT; s++) {
+            if (s > 1 && (s > kb / 2 || tiles * s > 148)) break;
+            const int kps = (kb + s - 1) / s;
+            const int ns = (kb + kps - 1) / kps;
+            if (ns != s) continue;
+            const long slots = (long)max_clusters(mt, bn, s);
+            const long waves = (tiles + slots - 1) / slots;
+            const double ingest = (double)kps * (mt * 128 + bn) * BK * 2;            // bytes through one CTA's smem
+            const double chip = ingest * (double)(tiles < slots ? tiles : slots) * s;  // concurrent L2 -> SM traffic of a wave
+            double t_main = ingest / 110e3;                                          // us at ~110 GB/s per SM
+            if (chip / 10.0e6 > t_main) t_main = chip / 10.0e6;                      // or the ~10 TB/s L2 ceiling
+            const double part = (s > 1) ? (double)mt * 128 * bn * 4 * (STG_LD / 32.0) : 0.0;
+            const double t_epi = (s > 1) ? part / 120e3 + 1.0 + part / 70e3 : (double)mt * 128 * bn * 2 / 40e3;
+            const double cost = waves * (2.0 + t_main + t_epi);
+            if (cost < best_cost) {
+                best_cost = cost;
+                best.mt = mt; best.bn = bn; best.grid_x = gx; best.grid_y = gy; best.n_split = s; best.kb_per_split = kps;
+            }
+        }
+    }
+    return best;
+}
+
 }  // namespace
+
+static unsigned long long* g_gemm_dbg = nullptr;
+void gemm_set_debug_buffer(unsigned long long* p) { g_gemm_dbg = p; }
 
 int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* W, long ldw, void* out, long ldo,
                       const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,
@@ -322,7 +427,7 @@ int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* 
     if (M == 0) return 0;
     GemmPlan p = plan_gemm(M, N, K);
     if (p.n_split > 1) {
-        const long need = (long)p.grid_x * p.grid_y * p.n_split * (128L * p.mt) * p.bn * 4;
+        const long need = (long)p.grid_x * p.grid_y * p.n_split * (long)p.mt * (p.bn / 32) * UNIT_FLOATS * 4;
         if (workspace == nullptr || workspace_bytes < need) return B200_ERR_WORKSPACE;
     }
     CUtensorMap tmA, tmW;
@@ -340,10 +445,12 @@ int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* 
     g.partials = static_cast<float*>(workspace);
     g.kb_per_split = p.kb_per_split;
     g.n_split = p.n_split;
-    if (p.mt == 2 && p.bn == 256) return launch_cfg<2, 256>(p, tmA, tmW, g, stream);
-    if (p.mt == 1 && p.bn == 256) return launch_cfg<1, 256>(p, tmA, tmW, g, stream);
-    if (p.mt == 2) return launch_cfg<2, 32>(p, tmA, tmW, g, stream);
-    return launch_cfg<1, 32>(p, tmA, tmW, g, stream);
+    g.dbg = g_gemm_dbg;
+    if (p.mt == 2)
+        return p.bn == 256 ? launch_cfg<2, 256>(p, tmA, tmW, g, stream)
+               : p.bn == 128 ? launch_cfg<2, 128>(p, tmA, tmW, g, stream) : launch_cfg<2, 32>(p, tmA, tmW, g, stream);
+    return p.bn == 256 ? launch_cfg<1, 256>(p, tmA, tmW, g, stream)
+           : p.bn == 128 ? launch_cfg<1, 128>(p, tmA, tmW, g, stream) : launch_cfg<1, 32>(p, tmA, tmW, g, stream);
 }
 
 }  // namespace b200
@@ -356,3 +463,6 @@ extern "C" int b200_linear_f16(int M, int N, int K, const void* A, long lda, con
     return b200::linear_f16_launch(M, N, K, A, lda, W, ldw, out, ldo, bias, residual, epilogue, workspace, workspace_bytes,
                                    static_cast<cudaStream_t>(stream));
 }
+
+// Debug aid (not part of the public header): point the GEMM timeline probes at a device buffer of >= 8 * n_ctas uint64.
+extern "C" void b200_debug_gemm_probe(void* buf) { b200::gemm_set_debug_buffer(static_cast<unsigned long long*>(buf)); }
