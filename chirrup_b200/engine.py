@@ -1,0 +1,491 @@
+"""Continuous-batching driver over the B200 model: Chirrup's ``AsyncEngineCore`` / ``Worker`` contract
+(``/root/reference/chirrup/engine_core.py:60-332``, ``chirrup/worker.py:107-889``, ``chirrup/interface.py:31-142``,
+``chirrup/core_structure.py``) kept at the API level, with the state handling redesigned for the C ABI:
+
+* the worker owns one ``batch_state`` (``generate_zero_state(batch_size)``, worker.py:260) and a slot table with the
+  reference's ``StateCategory`` classes; but instead of physically swapping state rows so that each class is contiguous
+  (``_organize_batch`` / ``_switch_batch``, worker.py:304-383 — three 16.5 MiB copies per swap at 7.2B) the kernels take a
+  slot-index vector, so grouping is integer-only (``group_slots``; offsets identical to ``min_swaps_to_target_fast``);
+* decode step = ``forward`` over the DECODE + ONE_PREFILL slots with T = 1 (worker.py:671-742); prefill = up to
+  ``max_forward_seq_len_per_forward`` = 100 tokens of every SEQ slot, every ``decode_prefill_ratio`` = 5 decode steps
+  (worker.py:173-179, :744-776, :854-856); admission of at most ``max_prefill_count`` new tasks per loop (worker.py:143, :570-669);
+* greedy requests (top_k == 1 or temperature == 0 or top_p == 0) are sampled by the C-ABI argmax kernel with ONE batched D2H
+  per step instead of one ``.item()`` per slot (worker.py:738-740); other requests use a torch nucleus sampler after the
+  reference's penalty formula (worker.py:527-547, :719-728) — sampling is downstream of the hot path.
+
+One worker per GPU, all pulling from one task queue (engine_core.py:71, :135-153): request-level data parallelism, no collective.
+"""
+from __future__ import annotations
+
+import asyncio
+import enum
+import queue
+import threading
+import time
+import uuid
+from dataclasses import dataclass, field
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+DEFAULT_STOP_TOKENS = [0, 261, 24281]                      # core_structure.py:15
+DEFAULT_SAMPLING_CONFIG = {"temperature": 1.0, "top_p": 0.3, "top_k": 0, "presence_penalty": 0.5,
+                           "frequency_penalty": 0.5, "penalty_decay": 0.996, "max_tokens": 8192}   # core_structure.py:28-36
+
+
+class FinishReason(enum.IntEnum):                           # core_structure.py:39-58
+    STOP = 0
+    LENGTH = 1
+    ABORT = 2
+
+    def __str__(self):
+        return ("stop", "length", "abort")[self.value]
+
+
+class RequestStatus(enum.IntEnum):                          # core_structure.py:62-90
+    WAITING = enum.auto()
+    RUNNING = enum.auto()
+    FINISHED_STOPPED = enum.auto()
+    FINISHED_LENGTH_CAPPED = enum.auto()
+    FINISHED_ABORTED = enum.auto()
+
+    @staticmethod
+    def is_finished(status: "RequestStatus") -> bool:
+        return status > RequestStatus.RUNNING
+
+
+class StateCategory(enum.IntEnum):                          # worker.py:86-92 (same order: it defines the batch layout)
+    FORWARD_ONE_DECODE = enum.auto()
+    FORWARD_ONE_PREFILL = enum.auto()
+    FORWARD_ONE_SUSPENDED = enum.auto()
+    FORWARD_SEQ = enum.auto()
+    FINISHED = enum.auto()
+    EMPTY = enum.auto()
+
+
+def group_slots(categories: Sequence[StateCategory], elements: Optional[Sequence[StateCategory]] = None):
+    """Integer-only replacement of ``min_swaps_to_target_fast`` (worker.py:43-78).  Returns ``(groups, offsets)``:
+    ``groups[c]`` = slot indices currently in category c (ascending), ``offsets`` = the ``[(start, end), ...]`` ranges the
+    reference would obtain after physically sorting — identical values, but here no state row moves: the kernels are handed
+    ``groups[c]`` as their slot-index vector."""
+    elements = list(elements) if elements is not None else list(sorted(StateCategory))
+    groups: Dict[StateCategory, List[int]] = {c: [] for c in elements}
+    for i, c in enumerate(categories):
+        groups.setdefault(c, []).append(i)
+    offsets: List[Tuple[int, int]] = []
+    off = 0
+    for c in elements:
+        n = len(groups.get(c, []))
+        offsets.append((off, off + n))
+        off += n
+    return groups, offsets
+
+
+@dataclass
+class Task:                                                 # core_structure.py:93-180 (same field names)
+    prompt_str: str = ""
+    prefill_tokens: List[int] = field(default_factory=list)
+    state: Optional[List[torch.Tensor]] = None
+    task_id: Optional[str] = None
+    priority: int = 0
+    temperature: float = DEFAULT_SAMPLING_CONFIG["temperature"]
+    top_p: float = DEFAULT_SAMPLING_CONFIG["top_p"]
+    top_k: int = DEFAULT_SAMPLING_CONFIG["top_k"]
+    presence_penalty: float = DEFAULT_SAMPLING_CONFIG["presence_penalty"]
+    frequency_penalty: float = DEFAULT_SAMPLING_CONFIG["frequency_penalty"]
+    penalty_decay: float = DEFAULT_SAMPLING_CONFIG["penalty_decay"]
+    max_tokens: Optional[int] = DEFAULT_SAMPLING_CONFIG["max_tokens"]
+    stop_tokens: List[int] = field(default_factory=lambda: list(DEFAULT_STOP_TOKENS))
+    forbidden_tokens: List[int] = field(default_factory=list)
+    cache_prefill: bool = False
+    cache_prefill_padding: int = 0
+    return_logits: bool = False
+    output_queue: Any = None                                # thread-safe channel back to the asyncio side
+    task_event_queue: "queue.Queue" = field(default_factory=queue.Queue)
+    request_status: RequestStatus = field(init=False, default=RequestStatus.WAITING)
+    generated_tokens: List[int] = field(init=False, default_factory=list)
+
+    def __post_init__(self):
+        if self.task_id is None:
+            self.task_id = str(uuid.uuid4())
+
+    def is_finished(self) -> bool:
+        return RequestStatus.is_finished(self.request_status)
+
+    def is_greedy(self) -> bool:
+        return self.top_k == 1 or self.temperature == 0 or self.top_p == 0
+
+
+@dataclass
+class ModelLoadConfig:                                      # core_structure.py:182-232 (fields the worker reads)
+    model_path: str = ""
+    vocab_size: int = 65536
+    head_size: int = 64
+    state_dict: Optional[Dict[str, torch.Tensor]] = None    # synthetic checkpoints (no .pth on disk)
+    vocab_path: Optional[str] = None
+
+
+@dataclass
+class _Slot:
+    task: Optional[Task] = None
+    category: StateCategory = StateCategory.EMPTY
+    pending: List[int] = field(default_factory=list)        # prompt tokens not yet consumed
+    next_token: int = 0
+
+
+_MODEL_LOAD_LOCK = threading.Lock()                          # worker.py:82-83
+
+
+class IdTokenizer:
+    """Stand-in when no vocabulary file is available (synthetic runs): prompts are token-id lists, text is empty."""
+
+    def encode(self, s: str) -> List[int]:
+        return [int(t) for t in s.split()] if s.strip() else [0]
+
+    def decode(self, toks: Sequence[int]) -> str:
+        return ""
+
+
+class Worker:
+    """One continuous-batching worker bound to one GPU (worker.py:107-889)."""
+
+    def __init__(self, worker_id: str, gpu_id: Sequence[int], model_config: ModelLoadConfig, task_queue: "queue.Queue",
+                 master_event_queue: Optional["queue.Queue"] = None, worker_event_queue: Optional["queue.Queue"] = None,
+                 batch_size: int = 32, tokenizer=None, model=None):
+        self.worker_id, self.gpu_id, self.model_config = worker_id, list(gpu_id), model_config
+        self.task_queue, self.master_event_queue = task_queue, master_event_queue
+        self.worker_event_queue = worker_event_queue or queue.Queue()
+        self.batch_size = batch_size
+        self.max_prefill_count = max(batch_size // 8, 1)      # worker.py:143
+        self.min_forward_seq_len = 10                         # worker.py:173-179
+        self.max_forward_seq_len_per_forward = 100
+        self.decode_prefill_ratio = 5
+        self.tokenizer = tokenizer or IdTokenizer()
+        self.model = model
+        self.slots: List[_Slot] = [_Slot() for _ in range(batch_size)]
+        self.steps = {"decode": 0, "prefill": 0, "decode_tokens": 0, "prefill_tokens": 0}
+        self._occurrence = None
+        self._stop = False
+
+    # ------------------------------------------------------------------ init
+    def _init_worker(self):
+        if self.model is not None and getattr(self.model, "device", None) is not None \
+                and torch.device(self.model.device).type != "cuda":
+            self.device = torch.device(self.model.device)     # CPU test double of the model (host-logic tests)
+        else:
+            torch.cuda.set_device(self.gpu_id[0])             # worker.py:255-256
+            self.device = torch.device("cuda", self.gpu_id[0])
+        if self.model is None:
+            from .rwkv7 import RWKV_x070, make_args
+
+            with _MODEL_LOAD_LOCK:                            # worker.py:209
+                args = make_args(self.model_config.model_path, self.model_config.vocab_size, self.model_config.head_size)
+                self.model = RWKV_x070(args, state_dict=self.model_config.state_dict, device=self.device)
+        self.batch_state = self.model.generate_zero_state(self.batch_size)      # worker.py:260
+        self._out_host = torch.empty((self.batch_size,), dtype=torch.int32)
+        if self.device.type == "cuda":
+            self._out_host = self._out_host.pin_memory()
+        if self.master_event_queue is not None:
+            self.master_event_queue.put(("worker_loaded", self.worker_id))      # worker.py:186-202
+
+    # ------------------------------------------------------------------ slot table
+    def categories(self) -> List[StateCategory]:
+        return [s.category for s in self.slots]
+
+    def _classify(self, slot: _Slot) -> None:
+        """DECODE / ONE_PREFILL / SEQ by remaining prompt length vs min_forward_seq_len (worker.py:646-654)."""
+        n = len(slot.pending)
+        if n == 0:
+            slot.category = StateCategory.FORWARD_ONE_DECODE
+        elif n > self.min_forward_seq_len:
+            slot.category = StateCategory.FORWARD_SEQ
+        else:
+            slot.category = StateCategory.FORWARD_ONE_PREFILL
+
+    def _fill_task_pool(self) -> int:
+        """Admit waiting tasks into EMPTY slots, at most max_prefill_count per loop (worker.py:570-669)."""
+        from . import state_move
+
+        groups, _ = group_slots(self.categories())
+        free = groups[StateCategory.EMPTY]
+        budget = self.max_prefill_count - len(groups[StateCategory.FORWARD_SEQ])
+        admitted = 0
+        while free and budget > 0:
+            try:
+                task: Task = self.task_queue.get_nowait()
+            except queue.Empty:
+                break
+            pos = free.pop(0)
+            slot = self.slots[pos]
+            if task.state is None:
+                state_move.clear_slot(self.batch_state, pos)                     # generate_zero_state(1), worker.py:586-589
+            else:
+                state_move.inject_slot(self.batch_state, pos, task.state)        # task.state[i].cuda(), worker.py:591-597
+            if self._occurrence is not None:
+                self._occurrence[pos].zero_()
+            toks = list(task.prefill_tokens) or [0]
+            slot.task, slot.pending = task, toks
+            task.request_status = RequestStatus.RUNNING
+            self._classify(slot)
+            admitted += 1
+            budget -= 1
+        return admitted
+
+    # ------------------------------------------------------------------ forwards
+    def _state_for(self, idx: torch.Tensor):
+        el = self.batch_state[2][idx.long()].contiguous()
+        return [self.batch_state[0], self.batch_state[1], el], el
+
+    def _run_forward_seq(self) -> int:
+        """One prefill chunk over the SEQ group (worker.py:744-776): every slot contributes exactly T tokens, logits discarded."""
+        groups, _ = group_slots(self.categories())
+        seq = groups[StateCategory.FORWARD_SEQ]
+        if not seq:
+            return 0
+        T = min(self.max_forward_seq_len_per_forward, min(len(self.slots[p].pending) - 1 for p in seq))
+        toks = [self.slots[p].pending[:T] for p in seq]
+        idx = torch.tensor(seq, dtype=torch.int32, device=self.device)
+        st, el = self._state_for(idx)
+        self.model._step(self.model._tokens(toks), len(seq), T, st, False, want_logits=False, slot_idx=idx)
+        self.batch_state[2][idx.long()] = el
+        for p in seq:
+            s = self.slots[p]
+            del s.pending[:T]
+            self._classify(s)
+        self.steps["prefill"] += 1
+        self.steps["prefill_tokens"] += T * len(seq)
+        return T * len(seq)
+
+    def _sample(self, rows: List[int], logits: torch.Tensor) -> List[int]:
+        """Next token for each row of `logits` (row i belongs to slot rows[i]).  Greedy rows: the C-ABI argmax kernel and ONE
+        batched D2H.  Others: forbidden-token mask + presence/frequency penalties with decay (worker.py:527-547, :719-728),
+        temperature, nucleus top-p / top-k, multinomial — in torch, outside the hot path."""
+        from . import ops
+
+        n = len(rows)
+        if logits.is_cuda:
+            ids = ops.argmax(logits)
+            self._out_host[:n].copy_(ids, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            out = self._out_host[:n].tolist()
+        else:                                                                    # CPU test double of the model
+            out = logits.float().argmax(-1).tolist()
+        for i, p in enumerate(rows):
+            t = self.slots[p].task
+            if t is None or t.is_greedy():
+                continue
+            if self._occurrence is None:
+                self._occurrence = torch.zeros((self.batch_size, logits.shape[1]), dtype=torch.float32, device=logits.device)
+            occ = self._occurrence[p]
+            lg = logits[i].float()
+            if t.forbidden_tokens:
+                lg[torch.tensor(t.forbidden_tokens, device=lg.device)] -= 1e10
+            lg = lg - t.presence_penalty * (occ > 0).float() - t.frequency_penalty * occ
+            probs = torch.softmax(lg / max(t.temperature, 1e-6), dim=-1)
+            sp, si = torch.sort(probs, descending=True)
+            keep = (torch.cumsum(sp, 0) - sp) < t.top_p
+            if t.top_k > 0:
+                keep[t.top_k:] = False
+            keep[0] = True
+            sp = sp * keep
+            tok = int(si[torch.multinomial(sp / sp.sum(), 1)])
+            occ.mul_(t.penalty_decay)
+            occ[tok] += 1.0
+            out[i] = tok
+        return out
+
+    def _finish(self, pos: int, status: RequestStatus) -> None:
+        slot = self.slots[pos]
+        t = slot.task
+        t.request_status = status
+        if t.output_queue is not None:
+            reason = {RequestStatus.FINISHED_STOPPED: FinishReason.STOP, RequestStatus.FINISHED_LENGTH_CAPPED: FinishReason.LENGTH,
+                      RequestStatus.FINISHED_ABORTED: FinishReason.ABORT}[status]
+            t.output_queue.put_nowait(("finish", reason, t))
+        self.slots[pos] = _Slot()                                                # -> EMPTY
+
+    def _run_forward_one(self) -> int:
+        """One T = 1 step over the DECODE and ONE_PREFILL groups (worker.py:671-742)."""
+        groups, _ = group_slots(self.categories())
+        dec, pre = groups[StateCategory.FORWARD_ONE_DECODE], groups[StateCategory.FORWARD_ONE_PREFILL]
+        rows = dec + pre                                                         # decode rows first, like the reference's layout
+        if not rows:
+            return 0
+        toks = []
+        for p in rows:
+            s = self.slots[p]
+            toks.append([s.pending.pop(0) if s.pending else s.next_token])
+        idx = torch.tensor(rows, dtype=torch.int32, device=self.device)
+        st, el = self._state_for(idx)
+        logits = self.model._step(self.model._tokens(toks), len(rows), 1, st, False, slot_idx=idx)
+        self.batch_state[2][idx.long()] = el
+        sample_rows = [i for i, p in enumerate(rows) if not self.slots[p].pending]    # prompt fully consumed: logits count
+        if sample_rows:
+            sel = logits if len(sample_rows) == len(rows) else logits[torch.tensor(sample_rows, device=logits.device)]
+            new = self._sample([rows[i] for i in sample_rows], sel)
+            for i, tok in zip(sample_rows, new):
+                p = rows[i]
+                s, t = self.slots[p], self.slots[p].task
+                s.next_token = tok
+                s.category = StateCategory.FORWARD_ONE_DECODE
+                t.generated_tokens.append(tok)
+                if t.output_queue is not None:
+                    t.output_queue.put_nowait(("token", tok, self.tokenizer.decode([tok]),
+                                               logits[i].detach().clone() if t.return_logits else None))
+                if tok in t.stop_tokens:
+                    self._finish(p, RequestStatus.FINISHED_STOPPED)
+                elif t.max_tokens is not None and len(t.generated_tokens) >= t.max_tokens:
+                    self._finish(p, RequestStatus.FINISHED_LENGTH_CAPPED)
+        self.steps["decode"] += 1
+        self.steps["decode_tokens"] += len(sample_rows)
+        return len(rows)
+
+    def _process_events(self) -> None:
+        """Shutdown / abort signals (worker.py:385-405, :512-525)."""
+        try:
+            while True:
+                ev = self.worker_event_queue.get_nowait()
+                if ev == "shutdown" or (isinstance(ev, tuple) and ev and ev[0] == "shutdown"):
+                    self._stop = True
+        except queue.Empty:
+            pass
+        for pos, s in enumerate(self.slots):
+            if s.task is not None and not s.task.task_event_queue.empty():
+                try:
+                    if s.task.task_event_queue.get_nowait() == "abort":
+                        self._finish(pos, RequestStatus.FINISHED_ABORTED)
+                except queue.Empty:
+                    pass
+
+    def step(self) -> int:
+        """One iteration of the main loop (worker.py:793-889): events, admission, decode step, periodic prefill chunk."""
+        self._process_events()
+        self._fill_task_pool()
+        n = self._run_forward_one()
+        if self.steps["decode"] % self.decode_prefill_ratio == 0 or n == 0:      # worker.py:854-856
+            n += self._run_forward_seq()
+        return n
+
+    def start(self) -> None:
+        self._init_worker()
+        while not self._stop:
+            if self.step() == 0:
+                time.sleep(0.001)
+
+    def busy(self) -> bool:
+        return any(s.category != StateCategory.EMPTY for s in self.slots)
+
+
+# ------------------------------------------------------------------------------------------------ asyncio side
+class ThreadSafeAsyncQueue:
+    """Worker threads put, the event loop gets (engine_core.py:30-57)."""
+
+    def __init__(self, event_loop: asyncio.AbstractEventLoop):
+        self.loop = event_loop
+        self.queue: asyncio.Queue = asyncio.Queue()
+
+    def put_nowait(self, item) -> None:
+        self.loop.call_soon_threadsafe(self.queue.put_nowait, item)
+
+
+class AsyncEngineCompletion:
+    """Async iterator over one request's events (interface.py:31-142): yields ``("token", id, text, logits|None)`` and ends
+    after ``("finish", FinishReason, task)``."""
+
+    def __init__(self, task: Task, task_queue: "queue.Queue", channel: ThreadSafeAsyncQueue):
+        self.task, self._task_queue, self._channel = task, task_queue, channel
+        self.finish_reason: Optional[FinishReason] = None
+        self._started = False
+
+    def start(self) -> "AsyncEngineCompletion":
+        if not self._started:
+            self._started = True
+            self._task_queue.put(self.task)                                      # interface.py:95-98
+        return self
+
+    def __aiter__(self):
+        return self.start()
+
+    async def __anext__(self):
+        if self.finish_reason is not None:
+            raise StopAsyncIteration
+        ev = await self._channel.queue.get()
+        if ev[0] == "finish":
+            self.finish_reason = ev[1]
+            raise StopAsyncIteration
+        return ev
+
+    async def get_full_completion(self) -> List[int]:
+        toks = []
+        async for ev in self:
+            toks.append(ev[1])
+        return toks
+
+    def abort(self) -> None:
+        self.task.task_event_queue.put("abort")                                  # interface.py:140-142
+
+
+class AsyncEngineCore:
+    """engine_core.py:60-332: N worker threads (worker k on GPU k) pulling from one shared task queue."""
+
+    def __init__(self):
+        self.task_queue: "queue.Queue" = queue.Queue()
+        self.master_event_queue: "queue.Queue" = queue.Queue()
+        self.workers: List[Worker] = []
+        self.threads: List[threading.Thread] = []
+        self.is_initialized = False
+        self.is_shutdown = False
+        self.tokenizer = IdTokenizer()
+        self.event_loop: Optional[asyncio.AbstractEventLoop] = None
+
+    def init(self, worker_num: int, model_config: ModelLoadConfig, batch_size: int = 32, tokenizer=None,
+             load_timeout_s: float = 300.0) -> "asyncio.Task":
+        self.event_loop = asyncio.get_event_loop()
+        if tokenizer is not None:
+            self.tokenizer = tokenizer
+        for k in range(worker_num):                                              # engine_core.py:135-153
+            w = Worker(f"worker_{k}", [k], model_config, self.task_queue, self.master_event_queue, batch_size=batch_size,
+                       tokenizer=self.tokenizer)
+            th = threading.Thread(target=w.start, daemon=True, name=w.worker_id)
+            self.workers.append(w)
+            self.threads.append(th)
+            th.start()
+
+        async def wait_for_workers_loaded():                                     # engine_core.py:156-173
+            loaded, t0 = 0, time.time()
+            while loaded < worker_num:
+                try:
+                    ev = self.master_event_queue.get_nowait()
+                    if ev[0] == "worker_loaded":
+                        loaded += 1
+                except queue.Empty:
+                    if time.time() - t0 > load_timeout_s:
+                        raise TimeoutError("workers did not load in time")
+                    if any(not th.is_alive() for th in self.threads):
+                        raise RuntimeError("a worker thread died while loading")   # the reference would wait out the timeout
+                    await asyncio.sleep(0.05)
+            self.is_initialized = True
+
+        return asyncio.ensure_future(wait_for_workers_loaded())
+
+    def completion(self, prompt_str: str = "", prefill_tokens: Optional[List[int]] = None, state=None, **kw) -> AsyncEngineCompletion:
+        """engine_core.py:181-267 (same keyword names as ``Task``)."""
+        assert not (state is not None and prefill_tokens is None), "prefill_tokens cannot be None when state is not None"
+        if not self.is_initialized:
+            raise RuntimeError("Engine not initialized")
+        if self.is_shutdown:
+            raise RuntimeError("Engine has been shutdown")
+        if not prefill_tokens:
+            prefill_tokens = self.tokenizer.encode(prompt_str)
+        channel = ThreadSafeAsyncQueue(self.event_loop)
+        task = Task(prompt_str=prompt_str, prefill_tokens=list(prefill_tokens), state=state, output_queue=channel, **kw)
+        return AsyncEngineCompletion(task, self.task_queue, channel)
+
+    def shutdown(self) -> None:
+        """One shutdown event PER worker (the reference enqueues a single one, so only one of N workers exits cleanly —
+        engine_core.py:279-283)."""
+        self.is_shutdown = True
+        for w in self.workers:
+            w.worker_event_queue.put("shutdown")
+        for th in self.threads:
+            th.join(timeout=10)

@@ -1,0 +1,147 @@
+"""GPU: the continuous-batching driver on the real model; slot movement; the reference op names on our kernels."""
+import asyncio
+import queue
+
+import pytest
+import torch
+
+from chirrup_b200.synth import GEOMETRIES, make_checkpoint
+
+pytestmark = pytest.mark.gpu
+
+
+def _model(geom_name="small", seed=8):
+    from chirrup_b200.rwkv7 import RWKV_x070, make_args
+
+    geom = GEOMETRIES[geom_name]
+    raw = make_checkpoint(geom, seed=seed, recipe="trained_like")
+    return geom, RWKV_x070(make_args(), state_dict=raw)
+
+
+def _greedy_alone(m, prompt, n):
+    from chirrup_b200 import ops
+
+    st = m.generate_zero_state(1)
+    lg = m.forward_seq_batch([prompt], st)
+    out = []
+    for _ in range(n):
+        t = int(ops.argmax(lg)[0])
+        out.append(t)
+        lg = m.forward_seq_batch([[t]], st)
+    return out
+
+
+def test_worker_continuous_batching_matches_isolated_greedy():
+    """Requests of mixed prompt lengths (1 .. 230 tokens: one-token prefill, chunked prefill <= 100, decode) admitted over time
+    into 6 slots produce exactly the tokens each request produces alone (slot indirection, no physical swaps)."""
+    from chirrup_b200.engine import ModelLoadConfig, Task, Worker
+
+    geom, m = _model()
+    w = Worker("w0", [0], ModelLoadConfig(), queue.Queue(), batch_size=6, model=m)
+    w._init_worker()
+    g = torch.Generator().manual_seed(0)
+    lens = [1, 3, 9, 11, 40, 150, 230, 12, 2, 64]
+    prompts = [torch.randint(1, geom.vocab_size, (n,), generator=g).tolist() for n in lens]
+
+    class Sink:
+        def __init__(self):
+            self.items = []
+
+        def put_nowait(self, x):
+            self.items.append(x)
+
+    sinks = [Sink() for _ in prompts]
+    for p, s in zip(prompts, sinks):
+        w.task_queue.put(Task(prefill_tokens=p, output_queue=s, top_k=1, max_tokens=12, stop_tokens=[]))
+    for _ in range(2000):
+        w.step()
+        if not w.busy() and w.task_queue.empty():
+            break
+    assert not w.busy()
+    for p, s in zip(prompts, sinks):
+        got = [e[1] for e in s.items if e[0] == "token"]
+        assert got == _greedy_alone(m, p, 12), f"prompt len {len(p)}"
+    assert w.steps["prefill"] > 0 and max(c for c in [w.max_forward_seq_len_per_forward]) == 100
+
+
+def test_async_engine_core_end_to_end():
+    from chirrup_b200.engine import AsyncEngineCore, FinishReason, ModelLoadConfig
+
+    geom = GEOMETRIES["tiny"]
+    raw = make_checkpoint(geom, seed=1, recipe="trained_like")
+
+    async def main():
+        eng = AsyncEngineCore()
+        await eng.init(worker_num=1, model_config=ModelLoadConfig(state_dict=raw, vocab_size=geom.vocab_size), batch_size=8)
+        comps = [eng.completion(prefill_tokens=[5 + i, 9, 11], top_k=1, max_tokens=6, stop_tokens=[]) for i in range(12)]
+        outs = await asyncio.gather(*[c.get_full_completion() for c in comps])
+        eng.shutdown()
+        return outs, [c.finish_reason for c in comps], eng.workers[0].model
+
+    outs, reasons, m = asyncio.run(main())
+    assert all(len(o) == 6 for o in outs) and all(r == FinishReason.LENGTH for r in reasons)
+    for i, o in enumerate(outs):
+        assert o == _greedy_alone(m, [5 + i, 9, 11], 6)
+
+
+def test_slot_extract_inject_migrate_bit_exact():
+    from chirrup_b200 import state_move
+
+    geom, m = _model("tiny", 3)
+    a = m.generate_zero_state(5)
+    m.forward_seq_batch(torch.randint(1, geom.vocab_size, (5, 7), generator=torch.Generator().manual_seed(1)).tolist(), a)
+    packed = state_move.extract_slot(a, 3)
+    assert packed[0].shape[2] == 1 and packed[1].shape[1] == 1 and int(packed[2][0]) == 7
+    b = m.generate_zero_state(4)
+    state_move.inject_slot(b, 1, packed)
+    moved = state_move.migrate_slot(a, 2, b, 0)
+    torch.cuda.synchronize()
+    assert moved == state_move.slot_bytes(a)
+    assert torch.equal(b[0][:, :, 1], a[0][:, :, 3]) and torch.equal(b[1][:, 1], a[1][:, 3]) and int(b[2][1]) == 7
+    assert torch.equal(b[0][:, :, 0], a[0][:, :, 2]) and torch.equal(b[1][:, 0], a[1][:, 2])
+    # a request continued in its new slot gives the same logits as in the old one
+    la = m._step(m._tokens([[11]]), 1, 1, [a[0], a[1], a[2][3:4].clone()], False, slot_idx=torch.tensor([3], dtype=torch.int32, device="cuda"))
+    lb = m._step(m._tokens([[11]]), 1, 1, [b[0], b[1], b[2][1:2].clone()], False, slot_idx=torch.tensor([1], dtype=torch.int32, device="cuda"))
+    assert torch.equal(la, lb)
+    # host round trip (what Chirrup's state cache stores)
+    cpu = state_move.extract_slot(a, 3, device="cpu", non_blocking=False)
+    c = m.generate_zero_state(2)
+    state_move.inject_slot(c, 0, cpu, non_blocking=False)
+    assert torch.equal(c[1][:, 0], a[1][:, 3])
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_slot_migration_between_gpus_p2p():
+    from chirrup_b200 import state_move
+
+    geom, m = _model("tiny", 3)
+    a = m.generate_zero_state(3)
+    m.forward_seq_batch([[1, 2, 3], [4, 5, 6], [7, 8, 9]], a)
+    b = [t.to("cuda:1").zero_() for t in m.generate_zero_state(2)]
+    state_move.migrate_slot(a, 1, b, 0)
+    torch.cuda.synchronize(0)
+    torch.cuda.synchronize(1)
+    assert torch.equal(b[1][:, 0].cpu(), a[1][:, 1].cpu()) and int(b[2][0]) == 3
+
+
+def test_reference_op_names_run_on_our_kernels():
+    """torch.ops.rwkv7_state_fwd_fp16.{forward_seq,forward_one,spmv_forward} (reference .cpp:21-25) registered by
+    chirrup_b200.torch_ops give the same bits as the direct C-ABI path."""
+    from chirrup_b200 import ops, torch_ops
+    from wkv_inputs import make_wkv_inputs
+
+    torch_ops.register()
+    B, T, H = 3, 4, 2
+    C = H * 64
+    st, r, w, k, v, a, b = [t.cuda() for t in make_wkv_inputs(B, T, H, seed=2)]
+    et = torch.tensor([0, 5, 9], dtype=torch.int32, device="cuda")
+    s1, s2 = st.clone(), st.clone()
+    y1 = ops.wkv7_forward_seq(s1, r, w, k, v, a, b, et)
+    y2 = torch.empty_like(r)
+    torch.ops.rwkv7_state_fwd_fp16.forward_seq(B, T, C, H, s2, r, w, k, v, a, b, y2, et)
+    assert torch.equal(y1, y2) and torch.equal(s1, s2)
+    vec = torch.relu(torch.randn(512, device="cuda") - 0.5).half()
+    mat = (torch.randn(512, 256, device="cuda") * 0.1).half()
+    out = torch.zeros(256, dtype=torch.float16, device="cuda")
+    torch.ops.rwkv7_state_fwd_fp16.spmv_forward(512, 256, vec, mat, out)
+    assert torch.equal(out, ops.spmv_forward(vec, mat))
