@@ -168,13 +168,39 @@ class RWKV_x070:
             return idxs.to(device=self.device, dtype=torch.int32, non_blocking=True).reshape(-1).contiguous()
         return torch.tensor(idxs, dtype=torch.int32).reshape(-1).to(self.device, non_blocking=True)
 
+    # Long prompts are processed in chunks of at most this many tokens per call (B * T_chunk): the WKV kernel carries each
+    # sequence's state from chunk to chunk through HBM, so the result is bit-identical to one long call, while the activation
+    # workspace stays bounded (23 buffers of tokens x C fp16).  The reference instead caps T at 100 in the worker
+    # (chirrup/worker.py:177) and runs whatever T it is given in one go.
+    max_tokens_per_step = 16384
+
     def forward_seq_batch(self, idxs: Sequence[Sequence[int]], state: List[torch.Tensor], full_output: bool = False):
         """rwkv7.py:351-382 — rectangular (B,T) token lists, batched state, logits (B,V) or (B,T,V)."""
         B = len(idxs)
         T = len(idxs[0]) if B else 0
         if B == 0:
             return torch.empty((0, self.vocab_size), dtype=DTYPE, device=self.device)
-        return self._step(self._tokens(idxs), B, T, state, full_output)
+        if full_output or B * T <= self.max_tokens_per_step:
+            return self._step(self._tokens(idxs), B, T, state, full_output)
+        return self.prefill(idxs, state)
+
+    def prefill(self, idxs, state: List[torch.Tensor], chunk_len: Optional[int] = None, want_logits: bool = True,
+                slot_idx: Optional[torch.Tensor] = None):
+        """Chunked prefill of B sequences x T tokens (config 4: 4k-token prompts, bsz 32): T is cut into chunks of
+        ``chunk_len`` tokens (default: as many as fit ``max_tokens_per_step``); only the last chunk computes ln_out + head.
+        Returns the last-token logits (B,V) (or None)."""
+        tok = idxs if torch.is_tensor(idxs) else torch.tensor(idxs, dtype=torch.int32)
+        tok = tok.to(device=self.device, dtype=torch.int32, non_blocking=True)
+        B, T = tok.shape
+        if chunk_len is None:
+            chunk_len = max(1, self.max_tokens_per_step // max(B, 1))
+        out = None
+        for t0 in range(0, T, chunk_len):
+            t1 = min(T, t0 + chunk_len)
+            last = t1 == T
+            out = self._step(tok[:, t0:t1].contiguous().view(-1), B, t1 - t0, state, False, want_logits=want_logits and last,
+                             slot_idx=slot_idx)
+        return out
 
     def forward_seq_batch_seperate(self, idxs, state, full_output: bool = False):
         """rwkv7.py:555-563 (the entry point Chirrup's worker calls, chirrup/worker.py:704, :775)."""

@@ -238,3 +238,33 @@ def test_prefill_chunking_invariance_of_integer_state_and_tolerance_of_float():
         lb = m.forward_seq_batch([[row[t]] for row in toks], sb)
     assert torch.equal(sa[2], sb[2])
     assert rel(la, lb) <= LOGIT_TOL and rel_l2(sa[1], sb[1]) <= STATE_TOL
+
+
+def test_chunked_prefill_and_state_cache_reuse():
+    """configs[3] at test size: prefill in chunks == prefill in one call (WKV state carried through HBM between chunks), and a
+    request resumed from a cached prefix state == the same request prefilled from scratch; elapsed counters bit-exact."""
+    from chirrup_b200 import state_move
+    from chirrup_b200.state_cache import StateCache
+
+    geom, raw, m = build("small", seed=6, recipe="trained_like")
+    B, T, P = 3, 50, 30
+    g = torch.Generator().manual_seed(4)
+    prefix = torch.randint(1, geom.vocab_size, (P,), generator=g)
+    toks = torch.cat([prefix.expand(B, -1), torch.randint(1, geom.vocab_size, (B, T - P), generator=g)], 1)
+    sa, sb = m.generate_zero_state(B), m.generate_zero_state(B)
+    la = m.forward_seq_batch(toks.tolist(), sa)
+    lb = m.prefill(toks, sb, chunk_len=7)
+    assert torch.equal(sa[2], sb[2]) and int(sa[2][0]) == T
+    assert rel(lb, la) <= LOGIT_TOL and rel_l2(sb[1], sa[1]) <= STATE_TOL and rel_l2(sb[0], sa[0]) <= STATE_TOL
+    cache = StateCache(max_gpu_entries=4)
+    s1 = m.generate_zero_state(1)
+    m.prefill(toks[:1, :P], s1, want_logits=False)
+    cache.put(prefix.tolist(), state_move.extract_slot(s1, 0))
+    sc = m.generate_zero_state(B)
+    for b in range(B):
+        n, packed = cache.get(toks[b].tolist(), max_len=T - 1)
+        assert n == P
+        state_move.inject_slot(sc, b, packed)
+    lc = m.prefill(toks[:, P:], sc)
+    assert torch.equal(sc[2], sa[2])
+    assert rel(lc, la) <= LOGIT_TOL and rel_l2(sc[1], sa[1]) <= STATE_TOL
