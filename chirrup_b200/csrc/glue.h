@@ -38,6 +38,17 @@ struct TmixPostArgs {
 };
 int launch_tmix_post(const TmixPostArgs& a, cudaStream_t s);
 
+// wkv7.cu: fused TMix core (prep + WKV-7 + GroupNorm/bonus/gate), inputs (B*T, C) fp16
+struct WkvFusedArgs {
+    int B, T, C, H, rows_per_slot;
+    const __half *r, *w, *k, *v, *a, *g, *vgate, *v_first;  // vgate / v_first == nullptr on layer 0
+    const __half *k_k, *k_a, *r_k, *ln_w, *ln_b;
+    __half* out;
+    const int* elapsed_t;
+    const int* slot_idx;
+};
+int launch_wkv7_fused(const WkvFusedArgs& a, void* state, long state_slot_stride, int n_slots, cudaStream_t stream);
+
 // gemm.cu
 int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* W, long ldw, void* out, long ldo,
                       const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,

@@ -104,6 +104,7 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
     if (!slot_idx) n_slots = B;
     int n = 0, rc = 0;
     static const bool debug_sync = getenv("B200_DEBUG_SYNC") != nullptr;
+    const bool unfused_tmix = getenv("B200_UNFUSED_TMIX") != nullptr;  // A/B switch: the three-kernel chain of glue.cu
 #define RUN(call)                                                                                     \
     do {                                                                                              \
         rc = (call);                                                                                  \
@@ -146,23 +147,36 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             RUN(lin(M, m->d_v, C, xv, w[B200_LW_V1], ws.lora, nullptr, nullptr, B200_EPI_NONE));
             RUN(lin(M, C, m->d_v, ws.lora, w[B200_LW_V2], ws.vg, w[B200_LW_V0], nullptr, B200_EPI_SIGMOID));
         }
-        TmixPrepArgs pa;
-        pa.M = (int)M; pa.C = C;
-        pa.k = ws.k; pa.v = vbuf; pa.a = ws.a;
-        pa.vgate = l > 0 ? ws.vg : nullptr;
-        pa.v_first = l > 0 ? ws.vfirst : nullptr;
-        pa.k_k = w[B200_LW_K_K]; pa.k_a = w[B200_LW_K_A];
-        pa.k_out = ws.k2; pa.v_out = ws.v2; pa.a_out = ws.an; pa.b_out = ws.bn;
-        RUN(launch_tmix_prep(pa, st));
-        const __half* vv = l > 0 ? ws.v2 : ws.vfirst;
-        RUN(b200_wkv7_forward_seq(B, T, C, H, s1 + l * s1_layer_stride, (long)C * 64, n_slots, ws.r, ws.w, ws.k2, vv, ws.an,
-                                  ws.bn, ws.y, elapsed, slot_idx, st));
-        TmixPostArgs po;
-        po.M = (int)M; po.C = C;
-        po.y = ws.y; po.r = ws.r; po.k = ws.k2; po.v = vv; po.g = ws.g;
-        po.ln_w = w[B200_LW_LNX_W]; po.ln_b = w[B200_LW_LNX_B]; po.r_k = w[B200_LW_R_K];
-        po.out = ws.yg;
-        RUN(launch_tmix_post(po, st));
+        if (!unfused_tmix) {
+            // prep + WKV-7 + GroupNorm/bonus/gate in one kernel per (sequence, head) tile
+            WkvFusedArgs fa;
+            fa.B = B; fa.T = T; fa.C = C; fa.H = H; fa.rows_per_slot = 0;
+            fa.r = ws.r; fa.w = ws.w; fa.k = ws.k; fa.v = vbuf; fa.a = ws.a; fa.g = ws.g;
+            fa.vgate = l > 0 ? ws.vg : nullptr;
+            fa.v_first = l > 0 ? ws.vfirst : nullptr;
+            fa.k_k = w[B200_LW_K_K]; fa.k_a = w[B200_LW_K_A]; fa.r_k = w[B200_LW_R_K];
+            fa.ln_w = w[B200_LW_LNX_W]; fa.ln_b = w[B200_LW_LNX_B];
+            fa.out = ws.yg; fa.elapsed_t = elapsed; fa.slot_idx = slot_idx;
+            RUN(launch_wkv7_fused(fa, s1 + l * s1_layer_stride, (long)C * 64, n_slots, st));
+        } else {
+            TmixPrepArgs pa;
+            pa.M = (int)M; pa.C = C;
+            pa.k = ws.k; pa.v = vbuf; pa.a = ws.a;
+            pa.vgate = l > 0 ? ws.vg : nullptr;
+            pa.v_first = l > 0 ? ws.vfirst : nullptr;
+            pa.k_k = w[B200_LW_K_K]; pa.k_a = w[B200_LW_K_A];
+            pa.k_out = ws.k2; pa.v_out = ws.v2; pa.a_out = ws.an; pa.b_out = ws.bn;
+            RUN(launch_tmix_prep(pa, st));
+            const __half* vv = l > 0 ? ws.v2 : ws.vfirst;
+            RUN(b200_wkv7_forward_seq(B, T, C, H, s1 + l * s1_layer_stride, (long)C * 64, n_slots, ws.r, ws.w, ws.k2, vv, ws.an,
+                                      ws.bn, ws.y, elapsed, slot_idx, st));
+            TmixPostArgs po;
+            po.M = (int)M; po.C = C;
+            po.y = ws.y; po.r = ws.r; po.k = ws.k2; po.v = vv; po.g = ws.g;
+            po.ln_w = w[B200_LW_LNX_W]; po.ln_b = w[B200_LW_LNX_B]; po.r_k = w[B200_LW_R_K];
+            po.out = ws.yg;
+            RUN(launch_tmix_post(po, st));
+        }
         RUN(lin(M, C, C, ws.yg, w[B200_LW_OUTPUT], ws.x, nullptr, ws.x, B200_EPI_RESADD));
         // ---- CMix
         MixPtrs<1> mc;

@@ -9,6 +9,7 @@
 // buffer with one TMA store.  A slot-index vector lets the caller address state rows indirectly (no physical slot swaps).
 #include "common.cuh"
 #include "tmap.h"
+#include "glue.h"
 #include "../../include/chirrup_b200.h"
 
 namespace b200 {
@@ -158,6 +159,176 @@ __global__ void __launch_bounds__(HS) wkv7_seq_kernel(const __grid_constant__ CU
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Fused TMix core (decode and prefill): everything between the projection GEMMs and the output GEMM in one kernel —
+// kk = normalize(k*k_k), k-mix, v-mix, a = -kk, b = kk*a (rwkv7.py:632-637); the WKV recurrence above (:645); GroupNorm over the
+// head's 64 outputs (eps 64e-5), bonus (sum r*k*r_k) v and the gate (:647-649).  Same arithmetic, op for op, as the unfused
+// tmix_prep / wkv7_seq / tmix_post chain (glue.cu): every half op computed in fp32 and rounded (`hr`), WKV in fp16 half2.
+// While the 8 KiB state tile is in flight (TMA) the 64 threads of the CTA (thread i = channel i of the head = state row i)
+// compute the vector prep; nothing but the tile, 8 input rows of 128 B and one output row of 128 B touches HBM.
+DEVI float hr(float x) { return __half2float(__float2half_rn(x)); }
+
+struct FusedIn {
+    float r, w, k, v, a, g, vg, vf;
+};
+
+DEVI void fused_load(FusedIn& f, const WkvFusedArgs& p, size_t idx) {
+    f.r = __half2float(p.r[idx]); f.w = __half2float(p.w[idx]); f.k = __half2float(p.k[idx]); f.v = __half2float(p.v[idx]);
+    f.a = __half2float(p.a[idx]); f.g = __half2float(p.g[idx]);
+    if (p.v_first) {
+        f.vg = __half2float(p.vgate[idx]);
+        f.vf = __half2float(p.v_first[idx]);
+    }
+}
+
+__global__ void __launch_bounds__(HS, 12) wkv7_fused_kernel(const __grid_constant__ CUtensorMap tm_state, const WkvFusedArgs p) {
+    __shared__ __align__(1024) uint8_t tile[HS * HS * 2];
+    __shared__ __align__(16) __half sv[5][HS];  // w~, k, a, b, r of the current token
+    __shared__ float red[4][2];
+    __shared__ __align__(8) uint64_t bar;
+
+    const int T = p.T, C = p.C, H = p.H;
+    const int bb = blockIdx.x / H;
+    const int h = blockIdx.x - bb * H;
+    const int i = threadIdx.x;
+    const int wi = i >> 5;
+    const int slot = p.slot_idx ? p.slot_idx[bb] : bb;
+    const int row0 = slot * p.rows_per_slot + h * HS;
+
+    if (i == 0) {
+        mbar_init(&bar, 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    if (i == 0) {
+        mbar_arrive_expect_tx(&bar, HS * HS * 2);
+        tma_load_2d(tile, &tm_state, 0, row0, &bar);
+    }
+    const int t0 = p.elapsed_t[bb];
+    const int c = h * HS + i;
+    const float kk_w = __half2float(p.k_k[c]), ka_w = __half2float(p.k_a[c]), rk_w = __half2float(p.r_k[c]);
+    const float ln_w = __half2float(p.ln_w[c]), ln_b = __half2float(p.ln_b[c]);
+    size_t idx = (size_t)bb * T * C + c;
+    FusedIn cur;
+    fused_load(cur, p, idx);
+
+    __half2 S[HS / 2];
+    bool have_state = false;
+
+    for (int t = 0; t < T; t++) {
+        if (t) __syncthreads();  // previous token's readers are done with sv / red
+        // ---- vector prep (rwkv7.py:632-637)
+        const float q = hr(cur.k * kk_w);
+        const float k2 = hr(cur.k * hr(1.0f + hr(hr(cur.a - 1.0f) * ka_w)));
+        const float v2 = p.v_first ? hr(cur.v + hr(hr(cur.vf - cur.v) * cur.vg)) : cur.v;
+        const float bonus_i = hr(hr(cur.r * k2) * rk_w);
+        const float s0 = warp_sum(q * q), s1 = warp_sum(bonus_i);
+        if ((i & 31) == 0) red[0][wi] = s0, red[1][wi] = s1;
+        __syncthreads();
+        const float nrm = hr(sqrtf(red[0][0] + red[0][1]));
+        const float bonus = hr(red[1][0] + red[1][1]);
+        const float kk = hr(q / nrm);
+        sv[0][i] = decay_dither(__float2half_rn(cur.w), t0 + t);
+        sv[1][i] = __float2half_rn(k2);
+        sv[2][i] = __float2half_rn(-kk);
+        sv[3][i] = __float2half_rn(hr(kk * cur.a));
+        sv[4][i] = __float2half_rn(cur.r);
+        const __half vv = __float2half_rn(v2);
+        const float gate = cur.g;
+        __syncthreads();
+        const size_t oidx = idx;
+        if (t + 1 < T) {
+            idx += C;
+            fused_load(cur, p, idx);
+        }
+        if (!have_state) {  // the tile has had the whole prep to arrive
+            mbar_wait(&bar, 0);
+            const int4* rowp = reinterpret_cast<const int4*>(tile + i * 128);
+            const int sw = i & 7;
+#pragma unroll
+            for (int cc = 0; cc < 8; cc++) {
+                int4 qq = rowp[cc ^ sw];
+                S[4 * cc + 0] = *reinterpret_cast<__half2*>(&qq.x);
+                S[4 * cc + 1] = *reinterpret_cast<__half2*>(&qq.y);
+                S[4 * cc + 2] = *reinterpret_cast<__half2*>(&qq.z);
+                S[4 * cc + 3] = *reinterpret_cast<__half2*>(&qq.w);
+            }
+            have_state = true;
+        }
+        // ---- WKV-7 (identical to wkv7_seq_kernel)
+        const int4* wv = reinterpret_cast<const int4*>(sv[0]);
+        const int4* kv = reinterpret_cast<const int4*>(sv[1]);
+        const int4* av = reinterpret_cast<const int4*>(sv[2]);
+        const int4* bv = reinterpret_cast<const int4*>(sv[3]);
+        const int4* rv = reinterpret_cast<const int4*>(sv[4]);
+        __half2 acc = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+        for (int cc = 0; cc < 8; cc++) {
+            int4 qq = av[cc];
+            const __half2* pp = reinterpret_cast<const __half2*>(&qq);
+#pragma unroll
+            for (int u = 0; u < 4; u++) acc = __hfma2(pp[u], S[4 * cc + u], acc);
+        }
+        const __half2 sa2 = __half2half2(__hadd_rn(__low2half(acc), __high2half(acc)));
+        const __half2 vv2 = __half2half2(vv);
+        acc = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+        for (int cc = 0; cc < 8; cc++) {
+            int4 qw = wv[cc], qk = kv[cc], qb = bv[cc], qr = rv[cc];
+            const __half2* pw = reinterpret_cast<const __half2*>(&qw);
+            const __half2* pk = reinterpret_cast<const __half2*>(&qk);
+            const __half2* pb = reinterpret_cast<const __half2*>(&qb);
+            const __half2* pr = reinterpret_cast<const __half2*>(&qr);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                __half2 s = S[4 * cc + u];
+                __half2 d = __hmul2_rn(pk[u], vv2);
+                d = __hfma2(s, pw[u], d);
+                d = __hfma2(sa2, pb[u], d);
+                s = __hadd2_rn(s, d);
+                S[4 * cc + u] = s;
+                acc = __hfma2(s, pr[u], acc);
+            }
+        }
+        const float y = __half2float(__hadd_rn(__low2half(acc), __high2half(acc)));
+        // ---- GroupNorm over the head (two-pass fp32 statistics, eps 64e-5) + bonus + gate (rwkv7.py:647-649)
+        const float m0 = warp_sum(y);
+        if ((i & 31) == 0) red[2][wi] = m0;
+        __syncthreads();
+        const float mean = (red[2][0] + red[2][1]) * (1.0f / 64.0f);
+        const float d = y - mean;
+        const float q0 = warp_sum(d * d);
+        if ((i & 31) == 0) red[3][wi] = q0;
+        __syncthreads();
+        const float rstd = 1.0f / sqrtf((red[3][0] + red[3][1]) * (1.0f / 64.0f) + 64e-5f);
+        const float gn = hr(d * rstd * ln_w + ln_b);
+        const float o = hr(gn + hr(bonus * v2));
+        p.out[oidx] = __float2half_rn(hr(o * gate));
+    }
+
+    {
+        int4* rowp = reinterpret_cast<int4*>(tile + i * 128);
+        const int sw = i & 7;
+#pragma unroll
+        for (int cc = 0; cc < 8; cc++) {
+            int4 qq;
+            qq.x = *reinterpret_cast<int*>(&S[4 * cc + 0]);
+            qq.y = *reinterpret_cast<int*>(&S[4 * cc + 1]);
+            qq.z = *reinterpret_cast<int*>(&S[4 * cc + 2]);
+            qq.w = *reinterpret_cast<int*>(&S[4 * cc + 3]);
+            rowp[cc ^ sw] = qq;
+        }
+    }
+    fence_proxy_async();
+    __syncthreads();
+    if (i == 0) {
+        tma_store_2d(&tm_state, 0, row0, tile);
+        tma_store_commit();
+        tma_store_wait_read<0>();
+    }
+}
+
 }  // namespace
 
 int wkv7_make_state_tmap(CUtensorMap* tm, const void* state, int n_slots, int H, long state_slot_stride) {
@@ -165,6 +336,18 @@ int wkv7_make_state_tmap(CUtensorMap* tm, const void* state, int n_slots, int H,
     const uint64_t rows_per_slot = (uint64_t)state_slot_stride / HS;
     const uint64_t rows = (uint64_t)(n_slots - 1) * rows_per_slot + (uint64_t)H * HS;
     return make_tmap_2d_f16(tm, state, rows, HS, HS * 2, HS, HS, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+}
+
+int launch_wkv7_fused(const WkvFusedArgs& a, void* state, long state_slot_stride, int n_slots, cudaStream_t stream) {
+    if (a.B <= 0 || a.T <= 0) return 0;
+    if (a.H * HS != a.C) return B200_ERR_BAD_ARG;
+    CUtensorMap tm;
+    int rc = wkv7_make_state_tmap(&tm, state, a.slot_idx ? n_slots : a.B, a.H, state_slot_stride);
+    if (rc) return rc;
+    WkvFusedArgs p = a;
+    p.rows_per_slot = (int)(state_slot_stride / HS);
+    wkv7_fused_kernel<<<a.B * a.H, HS, 0, stream>>>(tm, p);
+    return (int)cudaGetLastError();
 }
 
 }  // namespace b200

@@ -268,3 +268,35 @@ def test_chunked_prefill_and_state_cache_reuse():
     lc = m.prefill(toks[:, P:], sc)
     assert torch.equal(sc[2], sa[2])
     assert rel(lc, la) <= LOGIT_TOL and rel_l2(sc[1], sa[1]) <= STATE_TOL
+
+
+def test_fused_tmix_core_equals_three_kernel_chain():
+    """The fused kernel (prep + WKV-7 + GroupNorm/bonus/gate) vs the unfused tmix_prep / wkv7_seq / tmix_post chain
+    (B200_UNFUSED_TMIX=1): same ops in the same order; only the 64-wide fp32 reductions associate differently, so the results
+    agree to fp16 rounding noise and the greedy tokens are identical, for decode (T = 1) and prefill (T > 1), with slot indirection."""
+    geom, raw, m = build("small", seed=12, recipe="trained_like")
+    B = 4
+    toks = torch.randint(1, geom.vocab_size, (B, 9), generator=torch.Generator().manual_seed(3)).tolist()
+    outs = {}
+    for mode in ("fused", "unfused"):
+        if mode == "unfused":
+            os.environ["B200_UNFUSED_TMIX"] = "1"
+        else:
+            os.environ.pop("B200_UNFUSED_TMIX", None)
+        try:
+            st = m.generate_zero_state(B + 2)
+            idx = torch.tensor([4, 0, 5, 2], dtype=torch.int32, device="cuda")
+            el = torch.zeros(B, dtype=torch.int32, device="cuda")
+            lg = m._step(m._tokens(toks), B, 9, [st[0], st[1], el], False, slot_idx=idx)
+            seq = []
+            for _ in range(5):
+                nxt = lg.float().argmax(-1)
+                seq.append(nxt.clone())
+                lg = m._step(nxt.to(torch.int32), B, 1, [st[0], st[1], el], False, slot_idx=idx)
+            outs[mode] = (lg, st, torch.stack(seq), el.clone())
+        finally:
+            os.environ.pop("B200_UNFUSED_TMIX", None)
+    (la, sa, ta, ea), (lb, sb, tb, eb) = outs["fused"], outs["unfused"]
+    assert torch.equal(ta, tb) and torch.equal(ea, eb)
+    assert rel(la, lb) <= 2e-3 and rel_l2(sa[1], sb[1]) <= 5e-4
+    assert torch.count_nonzero(sa[1][:, 1]) == 0 and torch.count_nonzero(sa[1][:, 3]) == 0   # untouched slots stay zero
