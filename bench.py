@@ -157,41 +157,54 @@ def build_model(geom_name: str, device):
 
 
 def time_wkv_kernel(m, geom, state, bsz, reps=5):
-    """Average device time of one WKV launch (T = 1) over the model's real per-layer state (L x bsz x 16 MiB-per-7.2B-slot >> L2),
-    CUDA events on the launching (current) stream."""
+    """Average device time of one launch (T = 1) of the step's HBM-roofline kernel — the fused TMix core (prep + WKV-7 +
+    GroupNorm/bonus/gate, b200_tmix_core_fused) — and of the plain WKV kernel (b200_wkv7_forward_seq), each over the model's real
+    per-layer state (L x bsz x 8 KiB tiles: 4 GiB at 7.2B/bsz 256 >> L2), replayed from a CUDA graph (so that host launch
+    overhead does not pollute the per-launch device time) and timed with CUDA events on the launching stream."""
     from chirrup_b200 import ops
 
     C, H, L = geom.n_embd, geom.n_head, geom.n_layer
     dev = state[1].device
     mk = lambda s: (torch.randn(bsz, 1, C, device=dev) * s).half()
-    r, k, v = mk(0.5), mk(0.5), mk(0.5)
+    r, k, v, g, vf = mk(0.5), mk(0.5), mk(0.5), mk(1.0), mk(0.5)
     w = (torch.randn(bsz, 1, C, device=dev) - 1).half()
+    a_sig, vg = torch.sigmoid(mk(1.0).float()).half(), torch.sigmoid(mk(1.0).float()).half()
     kk = torch.nn.functional.normalize(torch.randn(bsz, 1, H, 64, device=dev), dim=-1).view(bsz, 1, C)
     a, b = (-kk).half(), (kk * torch.sigmoid(torch.randn(bsz, 1, C, device=dev))).half()
+    vec = lambda mean, std: (torch.randn(C, device=dev) * std + mean).half()
+    k_k, k_a, r_k, ln_w, ln_b = vec(0.85, 0.1), vec(1.0, 0.1), vec(0.0, 0.1), vec(1.0, 0.05), vec(0.0, 0.02)
     y = torch.empty_like(r)
     et = torch.zeros(bsz, dtype=torch.int32, device=dev)
     scratch = state[1].clone()
-    run = lambda: [ops.wkv7_forward_seq(scratch[l], r, w, k, v, a, b, et, y=y) for l in range(L)]
-    run()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    g = torch.cuda.CUDAGraph()   # replay so that host launch overhead does not pollute the per-launch device time
-    s = torch.cuda.Stream()
-    s.wait_stream(torch.cuda.current_stream())
-    with torch.cuda.stream(s):
+    runs = {
+        "fused": lambda: [ops.tmix_core_fused(scratch[l], r, w, k, v, a_sig, g, vg, vf, k_k, k_a, r_k, ln_w, ln_b, et, out=y)
+                          for l in range(L)],
+        "plain": lambda: [ops.wkv7_forward_seq(scratch[l], r, w, k, v, a, b, et, y=y) for l in range(L)],
+    }
+    out = {}
+    for name, run in runs.items():
         run()
-        with torch.cuda.graph(g, stream=s):
+        torch.cuda.synchronize()
+        g_ = torch.cuda.CUDAGraph()
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
             run()
-    torch.cuda.current_stream().wait_stream(s)
-    g.replay()
-    torch.cuda.synchronize()
-    e0.record()
-    for _ in range(reps):
-        g.replay()
-    e1.record()
-    torch.cuda.synchronize()
+            with torch.cuda.graph(g_, stream=s):
+                run()
+        torch.cuda.current_stream().wait_stream(s)
+        g_.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            g_.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = e0.elapsed_time(e1) * 1e-3 / (reps * L)
+        del g_
     del scratch
-    return e0.elapsed_time(e1) * 1e-3 / (reps * L)
+    return out
 
 
 def run_ours(a, rank, world, device):
@@ -274,7 +287,7 @@ def run_ours(a, rank, world, device):
     e2e_s = time.perf_counter() - t0
     barrier()
 
-    wkv_s = time_wkv_kernel(m, geom, state, B) if rank == 0 else 0.0
+    wkv_s = time_wkv_kernel(m, geom, state, B) if rank == 0 else {"fused": 0.0, "plain": 0.0}
     times = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=device)
     if world > 1:
         torch.distributed.all_reduce(times, op=torch.distributed.ReduceOp.MAX)
@@ -329,8 +342,14 @@ def main():
         value = n * a.bsz * a.steps / (r["ms"] * 1e-3)
         e2e = n * a.bsz * a.steps / (r["e2e_ms"] * 1e-3)
         g = r["geom"]
-        wkv_bytes = a.bsz * (2 * g.n_head * 64 * 64 * 2 + 7 * g.n_embd * 2 + 4)     # SURVEY.md §8(d), per launch (one layer)
-        achieved = wkv_bytes / r["wkv_s"] / 1e9
+        # algorithmic bytes per launch (one layer, bsz units): SURVEY.md §8(d) per-unit figure for the WKV op — state read + write,
+        # r,w,k,v,a,b in, y out, elapsed_t; the fused kernel on the path really reads 8 rows (r,w,k,v,a,g,vgate,v_first) and
+        # writes one (stated explicitly, as §8(d) asks of fused kernels).
+        state_bytes = a.bsz * 2 * g.n_head * 64 * 64 * 2
+        wkv_bytes = state_bytes + a.bsz * (7 * g.n_embd * 2 + 4)
+        fused_bytes = state_bytes + a.bsz * (9 * g.n_embd * 2 + 4)
+        achieved = fused_bytes / r["wkv_s"]["fused"] / 1e9
+        achieved_plain = wkv_bytes / r["wkv_s"]["plain"] / 1e9
         traffic = None
         try:
             traffic = json.load(open(os.path.join(ROOT, "profiles", "wkv_traffic.json"))).get(f"{a.geom}_bsz{a.bsz}")
@@ -342,13 +361,16 @@ def main():
             "e2e": {"value": e2e, "unit": "tok/s", "h2d_bytes_per_step": a.bsz * 4, "d2h_bytes_per_step": a.bsz * 4,
                     "api": "RWKV_x070.forward_seq_batch_seperate(host token ids) + greedy sample + D2H of the ids"},
             "gpu_launches": r["launches"], "cuda_graph": r["graph"], "clocks": r["clocks"],
-            "roofline": {"bound": "hbm", "kernel": "wkv7_seq_kernel (T=1)", "achieved": achieved, "peak": hbm_peak,
-                         "unit": "GB/s", "frac": achieved / hbm_peak, "frac_of_8TBps_nominal": achieved / 8000.0,
-                         "traffic": traffic, "peak_source": which, "algorithmic_bytes_per_launch": wkv_bytes,
-                         "us_per_launch": r["wkv_s"] * 1e6,
-                         "wkv_share_of_step": r["wkv_s"] * g.n_layer / (r["ms"] * 1e-3 / a.steps)},
+            "roofline": {"bound": "hbm", "kernel": "wkv7_fused_kernel (T=1): kk-normalise + k,v mix + WKV-7 state update + GroupNorm + bonus + gate",
+                         "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                         "frac_of_8TBps_nominal": achieved / 8000.0, "traffic": traffic, "peak_source": which,
+                         "algorithmic_bytes_per_launch": fused_bytes, "us_per_launch": r["wkv_s"]["fused"] * 1e6,
+                         "share_of_step": r["wkv_s"]["fused"] * g.n_layer / (r["ms"] * 1e-3 / a.steps),
+                         "plain_wkv_kernel": {"achieved": achieved_plain, "frac": achieved_plain / hbm_peak,
+                                              "algorithmic_bytes_per_launch": wkv_bytes,
+                                              "us_per_launch": r["wkv_s"]["plain"] * 1e6}},
             "gemm": {"flops_per_step": g.gemm_flops_per_token() * a.bsz,
-                     "achieved_tflops_if_rest_of_step": g.gemm_flops_per_token() * a.bsz / max(1e-9, (r["ms"] * 1e-3 / a.steps - r["wkv_s"] * g.n_layer)) / 1e12,
+                     "achieved_tflops_if_rest_of_step": g.gemm_flops_per_token() * a.bsz / max(1e-9, (r["ms"] * 1e-3 / a.steps - r["wkv_s"]["fused"] * g.n_layer)) / 1e12,
                      "peak_tflops": tf_peak},
         })
         if not a.skip_cpu_baseline and world == 1:

@@ -25,6 +25,7 @@ SIGNATURES: Dict[str, tuple] = {
     "b200_abi_version": (_I, []),
     "b200_wkv7_forward_seq": (_I, [_I, _I, _I, _I, _P, _L, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "b200_wkv7_forward_one": (_I, [_I, _I, _I, _P, _L, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "b200_tmix_core_fused": (_I, [_I, _I, _I, _I, _P, _L, _I] + [_P] * 17),
     "b200_spmv_forward": (_I, [_I, _I, _P, _P, _P, _P]),
     "b200_linear_f16": (_I, [_I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P, _I, _P, _L, _P]),
     "b200_linear_workspace_bytes": (_L, [_I, _I]),

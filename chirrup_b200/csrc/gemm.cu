@@ -125,9 +125,10 @@ DEVI void cluster_sync_all() {
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+// The body of one CTA: output tile (m0, n0) of problem `g`, K split blockIdx.z.  `tmAp` / `tmWp` point into kernel-parameter space.
 template <int MT, int BN>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
-    gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const GemmArgs g) {
+DEVI void gemm_body(const CUtensorMap* tmAp, const CUtensorMap* tmWp, const GemmArgs& g, const int n0, const int m0,
+                    const int tile_id) {
     using C = Cfg<MT, BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -138,8 +139,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int n0 = blockIdx.x * BN;
-    const int m0 = blockIdx.y * (128 * MT);
     const int split = blockIdx.z;
     const int kb_total = (g.K + BK - 1) / BK;
     const int kb0 = split * g.kb_per_split;
@@ -149,8 +148,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     PROBE(0);
 
     if (threadIdx.x == 0) {
-        tma_prefetch_desc(&tmA);
-        tma_prefetch_desc(&tmW);
+        tma_prefetch_desc(tmAp);
+        tma_prefetch_desc(tmWp);
         for (int s = 0; s < C::kStages; s++) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -166,7 +165,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
     PROBE(1);
 
     const int q = warp & 3;  // TMEM lane quarter of an epilogue warp
-    const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
 
     if (warp == 0) {
         if (lane == 0) {
@@ -181,8 +179,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
                 const int kc = (kb0 + it) * BK;
 #pragma unroll
                 for (int mt = 0; mt < MT; mt++)
-                    tma_load_2d_hint(st + mt * (128 * BK * 2), &tmA, kc, m0 + mt * 128, &full_bar[s], pol_a);
-                tma_load_2d_hint(st + C::kABytes, &tmW, kc, n0, &full_bar[s], pol_w);
+                    tma_load_2d_hint(st + mt * (128 * BK * 2), tmAp, kc, m0 + mt * 128, &full_bar[s], pol_a);
+                tma_load_2d_hint(st + C::kABytes, tmWp, kc, n0, &full_bar[s], pol_w);
             }
         }
         __syncwarp();
@@ -314,6 +312,32 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
         tc_fence_after();
         tmem_dealloc<C::kTmemCols>(tmem_base);
     }
+}
+
+template <int MT, int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+    gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const GemmArgs g) {
+    gemm_body<MT, BN>(&tmA, &tmW, g, blockIdx.x * BN, blockIdx.y * (128 * MT), blockIdx.y * gridDim.x + blockIdx.x);
+}
+
+// Several independent small problems sharing M, the tile shape and the K-split factor in ONE launch (the four LoRA
+// down-projections, then the four up-projections of a layer): blockIdx.x enumerates the N-tiles of all problems back to back.
+constexpr int MAX_GROUP = 4;
+struct alignas(64) GemmGroup {
+    CUtensorMap tmA[MAX_GROUP];
+    CUtensorMap tmW[MAX_GROUP];
+    GemmArgs g[MAX_GROUP];
+    int tile_end[MAX_GROUP];
+    int n;
+};
+
+template <int MT, int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_group_kernel(const __grid_constant__ GemmGroup grp) {
+    int p = 0;
+    while (p + 1 < grp.n && (int)blockIdx.x >= grp.tile_end[p]) p++;
+    const int local = blockIdx.x - (p ? grp.tile_end[p - 1] : 0);
+    gemm_body<MT, BN>(&grp.tmA[p], &grp.tmW[p], grp.g[p], local * BN, blockIdx.y * (128 * MT),
+                      blockIdx.y * gridDim.x + blockIdx.x);
 }
 
 struct GemmPlan {
@@ -451,6 +475,102 @@ int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* 
                : p.bn == 128 ? launch_cfg<2, 128>(p, tmA, tmW, g, stream) : launch_cfg<2, 32>(p, tmA, tmW, g, stream);
     return p.bn == 256 ? launch_cfg<1, 256>(p, tmA, tmW, g, stream)
            : p.bn == 128 ? launch_cfg<1, 128>(p, tmA, tmW, g, stream) : launch_cfg<1, 32>(p, tmA, tmW, g, stream);
+}
+
+template <int MT, int BN>
+static int launch_group_cfg(const GemmGroup& grp, int grid_x, int grid_y, int s, cudaStream_t stream) {
+    using C = Cfg<MT, BN>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_group_kernel<MT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+        if (e != cudaSuccess) return (int)e;
+        attr_done = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid_x, grid_y, s);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = C::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = s;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return (int)cudaLaunchKernelEx(&cfg, gemm_group_kernel<MT, BN>, grp);
+}
+
+// n <= 4 problems with the same M in one launch.  Falls back to one launch per problem when the group does not fit the
+// single-wave shapes it is meant for (large M).
+int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream) {
+    if (n <= 0 || M <= 0) return 0;
+    bool ok = n <= MAX_GROUP && M <= 256;
+    int max_n = 0, min_kb = 1 << 30;
+    for (int i = 0; i < n; i++) {
+        if ((d[i].K & 7) || (d[i].N & 7) || (d[i].lda & 7) || (d[i].ldw & 7) || (d[i].ldo & 7)) return B200_ERR_BAD_ARG;
+        if (d[i].N > max_n) max_n = d[i].N;
+        const int kb = (d[i].K + BK - 1) / BK;
+        if (kb < min_kb) min_kb = kb;
+    }
+    const int mt = (M > 128) ? 2 : 1;
+    const int bn = (max_n <= 512) ? 32 : 128;
+    int tiles = 0;
+    for (int i = 0; i < n; i++) tiles += (d[i].N + bn - 1) / bn;
+    if (tiles > 148) ok = false;
+    if (!ok) {
+        for (int i = 0; i < n; i++) {
+            int rc = linear_f16_launch(M, d[i].N, d[i].K, d[i].A, d[i].lda, d[i].W, d[i].ldw, d[i].out, d[i].ldo, d[i].bias,
+                                       d[i].residual, d[i].epi, workspace, workspace_bytes, stream);
+            if (rc) return rc;
+        }
+        return 0;
+    }
+    // common split factor: one wave, >= 2 K-blocks per split in every problem, no empty split in any problem
+    int s = 148 / tiles;
+    if (s > min_kb / 2) s = min_kb / 2;
+    if (s > MAX_SPLIT) s = MAX_SPLIT;
+    if (s < 1) s = 1;
+    for (; s > 1; s--) {
+        bool fits = tiles <= max_clusters(mt, bn, s);
+        for (int i = 0; i < n && fits; i++) {
+            const int kb = (d[i].K + BK - 1) / BK, kps = (kb + s - 1) / s;
+            if ((kb + kps - 1) / kps != s) fits = false;
+        }
+        if (fits) break;
+    }
+    if (s > 1) {
+        const long need = (long)tiles * s * mt * (bn / 32) * UNIT_FLOATS * 4;
+        if (workspace == nullptr || workspace_bytes < need) return B200_ERR_WORKSPACE;
+    }
+    GemmGroup grp;
+    grp.n = n;
+    int end = 0;
+    for (int i = 0; i < n; i++) {
+        int rc = make_tmap_2d_f16(&grp.tmA[i], d[i].A, (uint64_t)M, (uint64_t)d[i].K, (uint64_t)d[i].lda * 2, 128, BK,
+                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+        if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+        rc = make_tmap_2d_f16(&grp.tmW[i], d[i].W, (uint64_t)d[i].N, (uint64_t)d[i].K, (uint64_t)d[i].ldw * 2, bn, BK,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+        if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+        GemmArgs& g = grp.g[i];
+        g.M = M; g.N = d[i].N; g.K = d[i].K;
+        g.out = static_cast<__half*>(d[i].out);
+        g.ldo = d[i].ldo;
+        g.bias = static_cast<const __half*>(d[i].bias);
+        g.residual = static_cast<const __half*>(d[i].residual);
+        g.epi = d[i].epi;
+        g.partials = static_cast<float*>(workspace);
+        const int kb = (d[i].K + BK - 1) / BK;
+        g.kb_per_split = (kb + s - 1) / s;
+        g.n_split = s;
+        g.dbg = nullptr;
+        end += (d[i].N + bn - 1) / bn;
+        grp.tile_end[i] = end;
+    }
+    for (int i = n; i < MAX_GROUP; i++) grp.tile_end[i] = end;
+    if (mt == 2) return bn == 32 ? launch_group_cfg<2, 32>(grp, tiles, 1, s, stream) : launch_group_cfg<2, 128>(grp, tiles, 1, s, stream);
+    return bn == 32 ? launch_group_cfg<1, 32>(grp, tiles, 1, s, stream) : launch_group_cfg<1, 128>(grp, tiles, 1, s, stream);
 }
 
 }  // namespace b200

@@ -54,4 +54,19 @@ int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* 
                       const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,
                       cudaStream_t stream);
 
+struct LinearDesc {
+    int N, K;
+    const void* A;
+    long lda;
+    const void* W;
+    long ldw;
+    void* out;
+    long ldo;
+    const void* bias;
+    const void* residual;
+    int epi;
+};
+// Up to four linear layers sharing M in one launch (gemm.cu); larger groups / M fall back to one launch each.
+int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream);
+
 }  // namespace b200

@@ -25,7 +25,7 @@ inline long align_up(long x, long a) { return (x + a - 1) / a * a; }
 struct Ws {
     int* counters_and_partials;  // linear workspace
     long lin_bytes;
-    __half *x, *mix[6], *r, *k, *v, *w, *a, *g, *vg, *k2, *v2, *an, *bn, *y, *yg, *vfirst, *kx, *lora, *hidden, *xo;
+    __half *x, *mix[6], *r, *k, *v, *w, *a, *g, *vg, *k2, *v2, *an, *bn, *y, *yg, *vfirst, *kx, *lora[4], *hidden, *xo;
     long total;
 };
 
@@ -49,7 +49,7 @@ Ws carve(const b200_model* m, long M, void* base) {
     if (m->d_a > dmax) dmax = m->d_a;
     if (m->d_v > dmax) dmax = m->d_v;
     if (m->d_g > dmax) dmax = m->d_g;
-    ws.lora = reinterpret_cast<__half*>(take(M * align_up(dmax, 8) * 2));
+    for (int i = 0; i < 4; i++) ws.lora[i] = reinterpret_cast<__half*>(take(M * align_up(dmax, 8) * 2));
     ws.hidden = reinterpret_cast<__half*>(take(M * (long)m->F * 2));
     ws.total = off;
     return ws;
@@ -137,15 +137,22 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
         RUN(lin(M, C, C, xr, w[B200_LW_RECEPTANCE], ws.r, nullptr, nullptr, B200_EPI_NONE));
         RUN(lin(M, C, C, xk, w[B200_LW_KEY], ws.k, nullptr, nullptr, B200_EPI_NONE));
         RUN(lin(M, C, C, xv, w[B200_LW_VALUE], vbuf, nullptr, nullptr, B200_EPI_NONE));
-        RUN(lin(M, m->d_w, C, xw, w[B200_LW_W1], ws.lora, nullptr, nullptr, B200_EPI_TANH));
-        RUN(lin(M, C, m->d_w, ws.lora, w[B200_LW_W2], ws.w, w[B200_LW_W0], nullptr, B200_EPI_NONE));
-        RUN(lin(M, m->d_a, C, xa, w[B200_LW_A1], ws.lora, nullptr, nullptr, B200_EPI_NONE));
-        RUN(lin(M, C, m->d_a, ws.lora, w[B200_LW_A2], ws.a, w[B200_LW_A0], nullptr, B200_EPI_SIGMOID));
-        RUN(lin(M, m->d_g, C, xg, w[B200_LW_G1], ws.lora, nullptr, nullptr, B200_EPI_SIGMOID));
-        RUN(lin(M, C, m->d_g, ws.lora, w[B200_LW_G2], ws.g, nullptr, nullptr, B200_EPI_NONE));
-        if (l > 0) {
-            RUN(lin(M, m->d_v, C, xv, w[B200_LW_V1], ws.lora, nullptr, nullptr, B200_EPI_NONE));
-            RUN(lin(M, C, m->d_v, ws.lora, w[B200_LW_V2], ws.vg, w[B200_LW_V0], nullptr, B200_EPI_SIGMOID));
+        // the four LoRA down-projections in one grouped launch, then the four up-projections in another
+        // (w: tanh, +w0 ; a: +a0, sigmoid ; g: sigmoid inside ; v-gate: +v0, sigmoid — rwkv7.py:626, :629, :630, :637)
+        {
+            const int nl = (l > 0) ? 4 : 3;
+            LinearDesc dn[4] = {
+                {m->d_w, C, xw, C, w[B200_LW_W1], C, ws.lora[0], m->d_w, nullptr, nullptr, B200_EPI_TANH},
+                {m->d_a, C, xa, C, w[B200_LW_A1], C, ws.lora[1], m->d_a, nullptr, nullptr, B200_EPI_NONE},
+                {m->d_g, C, xg, C, w[B200_LW_G1], C, ws.lora[2], m->d_g, nullptr, nullptr, B200_EPI_SIGMOID},
+                {m->d_v, C, xv, C, w[B200_LW_V1], C, ws.lora[3], m->d_v, nullptr, nullptr, B200_EPI_NONE}};
+            RUN(linear_group_launch(nl, dn, (int)M, ws.counters_and_partials, ws.lin_bytes, st));
+            LinearDesc up[4] = {
+                {C, m->d_w, ws.lora[0], m->d_w, w[B200_LW_W2], m->d_w, ws.w, C, w[B200_LW_W0], nullptr, B200_EPI_NONE},
+                {C, m->d_a, ws.lora[1], m->d_a, w[B200_LW_A2], m->d_a, ws.a, C, w[B200_LW_A0], nullptr, B200_EPI_SIGMOID},
+                {C, m->d_g, ws.lora[2], m->d_g, w[B200_LW_G2], m->d_g, ws.g, C, nullptr, nullptr, B200_EPI_NONE},
+                {C, m->d_v, ws.lora[3], m->d_v, w[B200_LW_V2], m->d_v, ws.vg, C, w[B200_LW_V0], nullptr, B200_EPI_SIGMOID}};
+            RUN(linear_group_launch(nl, up, (int)M, ws.counters_and_partials, ws.lin_bytes, st));
         }
         if (!unfused_tmix) {
             // prep + WKV-7 + GroupNorm/bonus/gate in one kernel per (sequence, head) tile

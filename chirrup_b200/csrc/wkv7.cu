@@ -292,41 +292,39 @@ __global__ void __launch_bounds__(HS, 12) wkv7_fused_kernel(const __grid_constan
             }
         }
         const float y = __half2float(__hadd_rn(__low2half(acc), __high2half(acc)));
-        // ---- GroupNorm over the head (two-pass fp32 statistics, eps 64e-5) + bonus + gate (rwkv7.py:647-649)
-        const float m0 = warp_sum(y);
-        if ((i & 31) == 0) red[2][wi] = m0;
+        if (t == T - 1) {
+            // last token: send the new state on its way (registers -> swizzled tile -> one TMA store) BEFORE the output math, so
+            // that the write-back drains while the GroupNorm / bonus / gate reductions run
+            int4* rowp = reinterpret_cast<int4*>(tile + i * 128);
+            const int sw = i & 7;
+#pragma unroll
+            for (int cc = 0; cc < 8; cc++) {
+                int4 qq;
+                qq.x = *reinterpret_cast<int*>(&S[4 * cc + 0]);
+                qq.y = *reinterpret_cast<int*>(&S[4 * cc + 1]);
+                qq.z = *reinterpret_cast<int*>(&S[4 * cc + 2]);
+                qq.w = *reinterpret_cast<int*>(&S[4 * cc + 3]);
+                rowp[cc ^ sw] = qq;
+            }
+            fence_proxy_async();
+        }
+        // ---- GroupNorm over the head (fp32 statistics from one pass: sum and sum of squares; eps 64e-5) + bonus + gate
+        //      (rwkv7.py:647-649)
+        const float m0 = warp_sum(y), m1 = warp_sum(y * y);
+        if ((i & 31) == 0) red[2][wi] = m0, red[3][wi] = m1;
         __syncthreads();
+        if (t == T - 1 && i == 0) {
+            tma_store_2d(&tm_state, 0, row0, tile);
+            tma_store_commit();
+        }
         const float mean = (red[2][0] + red[2][1]) * (1.0f / 64.0f);
-        const float d = y - mean;
-        const float q0 = warp_sum(d * d);
-        if ((i & 31) == 0) red[3][wi] = q0;
-        __syncthreads();
-        const float rstd = 1.0f / sqrtf((red[3][0] + red[3][1]) * (1.0f / 64.0f) + 64e-5f);
-        const float gn = hr(d * rstd * ln_w + ln_b);
+        const float var = fmaxf((red[3][0] + red[3][1]) * (1.0f / 64.0f) - mean * mean, 0.0f);
+        const float rstd = 1.0f / sqrtf(var + 64e-5f);
+        const float gn = hr((y - mean) * rstd * ln_w + ln_b);
         const float o = hr(gn + hr(bonus * v2));
         p.out[oidx] = __float2half_rn(hr(o * gate));
     }
-
-    {
-        int4* rowp = reinterpret_cast<int4*>(tile + i * 128);
-        const int sw = i & 7;
-#pragma unroll
-        for (int cc = 0; cc < 8; cc++) {
-            int4 qq;
-            qq.x = *reinterpret_cast<int*>(&S[4 * cc + 0]);
-            qq.y = *reinterpret_cast<int*>(&S[4 * cc + 1]);
-            qq.z = *reinterpret_cast<int*>(&S[4 * cc + 2]);
-            qq.w = *reinterpret_cast<int*>(&S[4 * cc + 3]);
-            rowp[cc ^ sw] = qq;
-        }
-    }
-    fence_proxy_async();
-    __syncthreads();
-    if (i == 0) {
-        tma_store_2d(&tm_state, 0, row0, tile);
-        tma_store_commit();
-        tma_store_wait_read<0>();
-    }
+    if (i == 0) tma_store_wait_read<0>();  // the tile must stay valid until the bulk store has read it
 }
 
 }  // namespace
@@ -379,3 +377,19 @@ extern "C" int b200_wkv7_forward_one(int B, int C, int H, void* state, long stat
 }
 
 extern "C" int b200_abi_version(void) { return 1; }
+
+extern "C" int b200_tmix_core_fused(int B, int T, int C, int H, void* state, long state_slot_stride, int n_slots, const void* r,
+                                    const void* w, const void* k, const void* v, const void* a, const void* g,
+                                    const void* vgate, const void* v_first, const void* k_k, const void* k_a, const void* r_k,
+                                    const void* ln_w, const void* ln_b, void* out, const int* elapsed_t, const int* slot_idx,
+                                    void* stream) {
+    if (B < 0 || T < 0 || H <= 0 || H * HS != C) return B200_ERR_BAD_ARG;
+    if ((v_first == nullptr) != (vgate == nullptr)) return B200_ERR_BAD_ARG;
+    auto h = [](const void* p) { return static_cast<const __half*>(p); };
+    WkvFusedArgs fa;
+    fa.B = B; fa.T = T; fa.C = C; fa.H = H; fa.rows_per_slot = 0;
+    fa.r = h(r); fa.w = h(w); fa.k = h(k); fa.v = h(v); fa.a = h(a); fa.g = h(g); fa.vgate = h(vgate); fa.v_first = h(v_first);
+    fa.k_k = h(k_k); fa.k_a = h(k_a); fa.r_k = h(r_k); fa.ln_w = h(ln_w); fa.ln_b = h(ln_b);
+    fa.out = static_cast<__half*>(out); fa.elapsed_t = elapsed_t; fa.slot_idx = slot_idx;
+    return launch_wkv7_fused(fa, state, state_slot_stride, n_slots, static_cast<cudaStream_t>(stream));
+}

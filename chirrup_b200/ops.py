@@ -127,3 +127,22 @@ def argmax(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
     rc = _lib.lib().b200_argmax_f16(B, V, logits.data_ptr(), logits.stride(0), out.data_ptr(), _stream(logits))
     _lib.check(rc, "b200_argmax_f16")
     return out
+
+
+def tmix_core_fused(state, r, w, k, v, a, g, vgate, v_first, k_k, k_a, r_k, ln_w, ln_b, elapsed_t, slot_idx=None, out=None):
+    """The fused TMix core (``b200_tmix_core_fused``): inputs (B,T,C) fp16, per-channel vectors (C,), state (n_slots,H,64,64)
+    updated in place; ``vgate`` / ``v_first`` None on layer 0.  Returns (B,T,C)."""
+    B, T, C = r.shape
+    H = C // HEAD
+    if out is None:
+        out = torch.empty((B, T, C), dtype=torch.float16, device=r.device)
+    for n, t in (("state", state), ("r", r), ("w", w), ("k", k), ("v", v), ("a", a), ("g", g)):
+        _req(t, n)
+    p = lambda t: 0 if t is None else t.contiguous().data_ptr()
+    n_slots = state.shape[0]
+    stride = state.stride(0) if n_slots > 1 else C * HEAD
+    rc = _lib.lib().b200_tmix_core_fused(B, T, C, H, state.data_ptr(), stride, n_slots, p(r), p(w), p(k), p(v), p(a), p(g),
+                                         p(vgate), p(v_first), p(k_k), p(k_a), p(r_k), p(ln_w), p(ln_b), out.data_ptr(),
+                                         elapsed_t.data_ptr(), p(slot_idx), _stream(r))
+    _lib.check(rc, "b200_tmix_core_fused")
+    return out

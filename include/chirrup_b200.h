@@ -51,6 +51,20 @@ int b200_wkv7_forward_one(int B, int C, int H, void* state, long state_slot_stri
                           const int* elapsed_t, const int* slot_idx, void* stream);
 
 /*
+ * Fused TMix core: everything between the projection GEMMs and the output GEMM of RWKV_x070_TMix_seq_batch
+ * (Albatross/rwkv7.py:632-649) in ONE kernel per (sequence, head) tile:
+ *   kk = normalize(k*k_k) per head; k' = k*(1+(a-1)*k_a); v' = v + (v_first - v)*vgate (skipped when v_first == NULL: layer 0);
+ *   y = WKV7(state, r, w, k', v', -kk, kk*a)  [as b200_wkv7_forward_seq];  out = (GroupNorm_head(y; eps 64e-5)*ln_w + ln_b
+ *   + (sum_head r*k'*r_k) v') * g.
+ * r,w,k,v,a,g,vgate,v_first,out: fp16 (B,T,C); a and vgate already sigmoid-ed; k_k,k_a,r_k,ln_w,ln_b: fp16 (C).
+ * State arguments as in b200_wkv7_forward_seq.  This is the HBM-roofline kernel of the decode step.
+ */
+int b200_tmix_core_fused(int B, int T, int C, int H, void* state, long state_slot_stride, int n_slots, const void* r,
+                         const void* w, const void* k, const void* v, const void* a, const void* g, const void* vgate,
+                         const void* v_first, const void* k_k, const void* k_a, const void* r_k, const void* ln_w,
+                         const void* ln_b, void* out, const int* elapsed_t, const int* slot_idx, void* stream);
+
+/*
  * out[c] = sum_d vec[d] * mat[d*C + c], skipping rows with vec[d] == 0 (ReLU^2 sparsity of the FFN key).
  * vec (D) fp16, mat (D,C) fp16 row-major, out (C) fp16 — overwritten (no pre-zeroing needed, unlike the reference).
  * fp32 accumulation in a fixed order: deterministic, one rounding.
