@@ -29,6 +29,7 @@ SIGNATURES: Dict[str, tuple] = {
     "b200_spmv_forward": (_I, [_I, _I, _P, _P, _P, _P]),
     "b200_linear_f16": (_I, [_I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P, _I, _P, _L, _P]),
     "b200_linear_workspace_bytes": (_L, [_I, _I]),
+    "b200_linear_group_f16": (_I, [_I, _P, _I, _P, _L, _P]),
     "b200_layer_norm_f16": (_I, [_I, _I, _P, _P, _P, _P, _P]),
     "b200_model_create": (_I, [_I, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "b200_model_destroy": (None, [_P]),
@@ -37,6 +38,12 @@ SIGNATURES: Dict[str, tuple] = {
     "b200_model_last_launch_count": (_I, [_P]),
     "b200_argmax_f16": (_I, [_I, _I, _P, _L, _P, _P]),
 }
+
+
+class LinearDesc(ctypes.Structure):
+    """``b200_linear_desc`` of include/chirrup_b200.h."""
+    _fields_ = [("N", _I), ("K", _I), ("A", _P), ("lda", _L), ("W", _P), ("ldw", _L), ("out", _P), ("ldo", _L),
+                ("bias", _P), ("residual", _P), ("epilogue", _I)]
 
 
 def header_symbols() -> List[str]:

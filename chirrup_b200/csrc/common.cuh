@@ -156,10 +156,47 @@ DEVI float rcp_approx_ftz(float x) {
     return y;
 }
 
+// ------------------------------------------------------------------ programmatic dependent launch (PDL)
+// Every kernel of the step calls pdl_launch_dependents() first (the next kernel of the stream may start its prologue while
+// this one runs) and pdl_wait() before it touches anything a predecessor wrote (returns once ALL prerequisite grids have
+// completed and flushed; a no-op when the launch carried no PDL attribute).  Every CTA must execute pdl_wait() so that
+// "this grid completed" keeps implying "its predecessors completed" down the chain.
+DEVI void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+DEVI void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 DEVI float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
+}
+
+// Host side: launch `kernel` with an optional programmatic-stream-serialization attribute (PDL) and an optional cluster
+// shape along z.  All kernels launched with pdl = true must call pdl_wait() in every CTA.
+template <typename... KArgs, typename... Args>
+static inline int launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, bool pdl,
+                                int cluster_z, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (cluster_z > 0) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = 1;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = cluster_z;
+        na++;
+    }
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    return (int)cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 }  // namespace b200

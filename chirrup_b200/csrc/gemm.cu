@@ -12,7 +12,10 @@
 // Decode-sized problems (M <= 256: a handful of tiles) are split along K over the CTAs of one thread-block CLUSTER: every CTA
 // parks its fp32 partial tile in an L2-resident workspace, the cluster barrier orders the writes, and then each CTA reduces and
 // finishes a 1/S share of the tile, summing the partials in split order (deterministic, no atomics, no spinning).
+#include <cstdlib>
+
 #include "common.cuh"
+#include "gemm_common.cuh"
 #include "glue.h"
 #include "tmap.h"
 #include "../../include/chirrup_b200.h"
@@ -20,10 +23,8 @@
 namespace b200 {
 namespace {
 
-constexpr int BK = 64;
 constexpr int GEMM_THREADS = 192;
 constexpr int MAX_SPLIT = 8;                      // portable cluster size
-constexpr int STG_LD = 36;  // row pitch (floats) of staged / parked 32-column units: 16-byte aligned rows, conflict-free 128-bit accesses
 constexpr int UNIT_FLOATS = 128 * STG_LD;         // one parked unit: 128 rows x 32 columns (+4 pad) fp32 = 18 KiB
 constexpr long WS_BYTES = 160L * 64 * UNIT_FLOATS * 4;  // > 148 CTAs x the largest tile (256 x 256 = 64 units)
 
@@ -36,70 +37,6 @@ struct Cfg {
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
     static constexpr uint32_t kTmemCols = (MT * BN) < 32 ? 32 : MT * BN;
     static constexpr int kUnits = MT * (BN / 32);  // epilogue work units of 128 rows x 32 columns
-};
-
-DEVI float round_h(float x) { return __half2float(__float2half_rn(x)); }
-
-template <int EPI>
-DEVI float epilogue_op(float acc, float bias, float res) {
-    if (EPI == B200_EPI_NONE) return acc + bias;
-    if (EPI == B200_EPI_TANH) return tanhf(round_h(acc + bias));
-    if (EPI == B200_EPI_SIGMOID)  // 1 / (1 + 2^(-x log2 e)) on the MUFU units: error ~1e-6 relative, far below the fp16 rounding
-        return rcp_approx_ftz(1.0f + ex2_approx_ftz(-1.4426950408889634f * round_h(acc + bias)));
-    if (EPI == B200_EPI_RELU_SQ) {
-        float t = fmaxf(round_h(acc), 0.0f);
-        return t * t;
-    }
-    return res + round_h(acc);  // B200_EPI_RESADD
-}
-
-// Four consecutive output columns of one row: fp32 -> epilogue -> fp16, one 8-byte store.  In the epilogue's coalesced
-// layout a warp instruction covers 4 rows x 64 contiguous bytes.
-template <int EPI>
-DEVI void finish4(const float4 acc, __half* __restrict__ out_row, const __half* __restrict__ bias,
-                  const __half* __restrict__ res_row, int c) {
-    float a[4] = {acc.x, acc.y, acc.z, acc.w};
-    float bv[4] = {0.f, 0.f, 0.f, 0.f}, rv[4] = {0.f, 0.f, 0.f, 0.f};
-    if ((EPI == B200_EPI_NONE || EPI == B200_EPI_TANH || EPI == B200_EPI_SIGMOID) && bias != nullptr) {
-        uint2 q = *reinterpret_cast<const uint2*>(bias + c);
-        const __half* p = reinterpret_cast<const __half*>(&q);
-#pragma unroll
-        for (int e = 0; e < 4; e++) bv[e] = __half2float(p[e]);
-    }
-    if (EPI == B200_EPI_RESADD) {
-        uint2 q = *reinterpret_cast<const uint2*>(res_row + c);
-        const __half* p = reinterpret_cast<const __half*>(&q);
-#pragma unroll
-        for (int e = 0; e < 4; e++) rv[e] = __half2float(p[e]);
-    }
-    uint2 o;
-    __half* po = reinterpret_cast<__half*>(&o);
-#pragma unroll
-    for (int e = 0; e < 4; e++) po[e] = __float2half_rn(epilogue_op<EPI>(a[e], bv[e], rv[e]));
-    *reinterpret_cast<uint2*>(out_row + c) = o;
-}
-
-DEVI void finish4_rt(int epi, const float4 acc, __half* out_row, const __half* bias, const __half* res_row, int c) {
-    switch (epi) {
-        case B200_EPI_NONE: finish4<B200_EPI_NONE>(acc, out_row, bias, res_row, c); break;
-        case B200_EPI_TANH: finish4<B200_EPI_TANH>(acc, out_row, bias, res_row, c); break;
-        case B200_EPI_SIGMOID: finish4<B200_EPI_SIGMOID>(acc, out_row, bias, res_row, c); break;
-        case B200_EPI_RELU_SQ: finish4<B200_EPI_RELU_SQ>(acc, out_row, bias, res_row, c); break;
-        default: finish4<B200_EPI_RESADD>(acc, out_row, bias, res_row, c); break;
-    }
-}
-
-struct GemmArgs {
-    int M, N, K;
-    __half* out;
-    long ldo;
-    const __half* bias;
-    const __half* residual;
-    int epi;
-    float* partials;  // [tile][split][unit][128][32] fp32
-    int kb_per_split;
-    int n_split;      // == cluster size along z
-    unsigned long long* dbg;  // optional timeline probe (globaltimer ns), 8 slots per CTA; nullptr in production
 };
 
 DEVI unsigned long long gtime() {
@@ -145,6 +82,7 @@ DEVI void gemm_body(const CUtensorMap* tmAp, const CUtensorMap* tmWp, const Gemm
     const int kb1 = min(kb_total, kb0 + g.kb_per_split);
     const int n_kb = kb1 - kb0;  // >= 1 by construction of the launch
     const bool splitk = g.n_split > 1;
+    pdl_launch_dependents();
     PROBE(0);
 
     if (threadIdx.x == 0) {
@@ -162,6 +100,7 @@ DEVI void gemm_body(const CUtensorMap* tmAp, const CUtensorMap* tmWp, const Gemm
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // everything above overlapped the previous kernel's tail; A / residual / workspace are touched only below
     PROBE(1);
 
     const int q = warp & 3;  // TMEM lane quarter of an epilogue warp
@@ -345,27 +284,13 @@ struct GemmPlan {
 };
 
 template <int MT, int BN>
-static int launch_cfg(const GemmPlan& p, const CUtensorMap& tmA, const CUtensorMap& tmW, const GemmArgs& g, cudaStream_t stream) {
+static int launch_cfg(const GemmPlan& p, const CUtensorMap& tmA, const CUtensorMap& tmW, const GemmArgs& g, cudaStream_t stream,
+                      bool pdl) {
     using C = Cfg<MT, BN>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_kernel<MT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
-        if (e != cudaSuccess) return (int)e;
-        attr_done = true;
-    }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(p.grid_x, p.grid_y, p.n_split);
-    cfg.blockDim = dim3(GEMM_THREADS);
-    cfg.dynamicSmemBytes = C::kSmemBytes;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 1;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = p.n_split;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    return (int)cudaLaunchKernelEx(&cfg, gemm_kernel<MT, BN>, tmA, tmW, g);
+    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<MT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    if (e != cudaSuccess) return (int)e;  // per device, cheap: set on every launch (one process may drive several GPUs)
+    return launch_kernel(gemm_kernel<MT, BN>, dim3(p.grid_x, p.grid_y, p.n_split), dim3(GEMM_THREADS), C::kSmemBytes, stream, pdl,
+                         p.n_split, tmA, tmW, g);
 }
 
 // How many clusters of `s` CTAs of this configuration the device can hold at once (GPC boundaries strand SMs for big clusters).
@@ -440,15 +365,24 @@ static GemmPlan plan_gemm(int M, int N, int K) {
 }  // namespace
 
 static unsigned long long* g_gemm_dbg = nullptr;
+static bool no_pair() {
+    static const bool v = getenv("B200_NO_PAIR") != nullptr;  // A/B switch: one-CTA tiles (this file) for every M
+    return v;
+}
 void gemm_set_debug_buffer(unsigned long long* p) { g_gemm_dbg = p; }
 
 int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* W, long ldw, void* out, long ldo,
                       const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,
-                      cudaStream_t stream) {
+                      cudaStream_t stream, bool pdl) {
     if (M < 0 || N <= 0 || K <= 0 || (K & 7) || (N & 7) || (lda & 7) || (ldw & 7) || (ldo & 7)) return B200_ERR_BAD_ARG;
     if (epilogue < B200_EPI_NONE || epilogue > B200_EPI_RESADD) return B200_ERR_BAD_ARG;
     if (epilogue == B200_EPI_RESADD && residual == nullptr) return B200_ERR_BAD_ARG;
     if (M == 0) return 0;
+    if (M > 128 && !no_pair()) {  // decode / prefill sized token counts: CTA pairs (gemm_pair.cu)
+        LinearDesc d1 = {N, K, A, lda, W, ldw, out, ldo, bias, residual, epilogue};
+        const int rc = pair_group_launch(1, &d1, M, workspace, workspace_bytes, stream, pdl, g_gemm_dbg);
+        if (rc != B200_ERR_UNSUPPORTED) return rc;
+    }
     GemmPlan p = plan_gemm(M, N, K);
     if (p.n_split > 1) {
         const long need = (long)p.grid_x * p.grid_y * p.n_split * (long)p.mt * (p.bn / 32) * UNIT_FLOATS * 4;
@@ -471,40 +405,28 @@ int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* 
     g.n_split = p.n_split;
     g.dbg = g_gemm_dbg;
     if (p.mt == 2)
-        return p.bn == 256 ? launch_cfg<2, 256>(p, tmA, tmW, g, stream)
-               : p.bn == 128 ? launch_cfg<2, 128>(p, tmA, tmW, g, stream) : launch_cfg<2, 32>(p, tmA, tmW, g, stream);
-    return p.bn == 256 ? launch_cfg<1, 256>(p, tmA, tmW, g, stream)
-           : p.bn == 128 ? launch_cfg<1, 128>(p, tmA, tmW, g, stream) : launch_cfg<1, 32>(p, tmA, tmW, g, stream);
+        return p.bn == 256 ? launch_cfg<2, 256>(p, tmA, tmW, g, stream, pdl)
+               : p.bn == 128 ? launch_cfg<2, 128>(p, tmA, tmW, g, stream, pdl) : launch_cfg<2, 32>(p, tmA, tmW, g, stream, pdl);
+    return p.bn == 256 ? launch_cfg<1, 256>(p, tmA, tmW, g, stream, pdl)
+           : p.bn == 128 ? launch_cfg<1, 128>(p, tmA, tmW, g, stream, pdl) : launch_cfg<1, 32>(p, tmA, tmW, g, stream, pdl);
 }
 
 template <int MT, int BN>
-static int launch_group_cfg(const GemmGroup& grp, int grid_x, int grid_y, int s, cudaStream_t stream) {
+static int launch_group_cfg(const GemmGroup& grp, int grid_x, int grid_y, int s, cudaStream_t stream, bool pdl) {
     using C = Cfg<MT, BN>;
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_group_kernel<MT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
-        if (e != cudaSuccess) return (int)e;
-        attr_done = true;
-    }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid_x, grid_y, s);
-    cfg.blockDim = dim3(GEMM_THREADS);
-    cfg.dynamicSmemBytes = C::kSmemBytes;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 1;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = s;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    return (int)cudaLaunchKernelEx(&cfg, gemm_group_kernel<MT, BN>, grp);
+    cudaError_t e = cudaFuncSetAttribute(gemm_group_kernel<MT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    if (e != cudaSuccess) return (int)e;
+    return launch_kernel(gemm_group_kernel<MT, BN>, dim3(grid_x, grid_y, s), dim3(GEMM_THREADS), C::kSmemBytes, stream, pdl, s, grp);
 }
 
 // n <= 4 problems with the same M in one launch.  Falls back to one launch per problem when the group does not fit the
 // single-wave shapes it is meant for (large M).
-int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream) {
+int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream, bool pdl) {
     if (n <= 0 || M <= 0) return 0;
+    if (M > 128 && !no_pair()) {
+        const int rc = pair_group_launch(n, d, M, workspace, workspace_bytes, stream, pdl, nullptr);
+        if (rc != B200_ERR_UNSUPPORTED) return rc;
+    }
     bool ok = n <= MAX_GROUP && M <= 256;
     int max_n = 0, min_kb = 1 << 30;
     for (int i = 0; i < n; i++) {
@@ -521,7 +443,7 @@ int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long
     if (!ok) {
         for (int i = 0; i < n; i++) {
             int rc = linear_f16_launch(M, d[i].N, d[i].K, d[i].A, d[i].lda, d[i].W, d[i].ldw, d[i].out, d[i].ldo, d[i].bias,
-                                       d[i].residual, d[i].epi, workspace, workspace_bytes, stream);
+                                       d[i].residual, d[i].epi, workspace, workspace_bytes, stream, pdl);
             if (rc) return rc;
         }
         return 0;
@@ -569,8 +491,8 @@ int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long
         grp.tile_end[i] = end;
     }
     for (int i = n; i < MAX_GROUP; i++) grp.tile_end[i] = end;
-    if (mt == 2) return bn == 32 ? launch_group_cfg<2, 32>(grp, tiles, 1, s, stream) : launch_group_cfg<2, 128>(grp, tiles, 1, s, stream);
-    return bn == 32 ? launch_group_cfg<1, 32>(grp, tiles, 1, s, stream) : launch_group_cfg<1, 128>(grp, tiles, 1, s, stream);
+    if (mt == 2) return bn == 32 ? launch_group_cfg<2, 32>(grp, tiles, 1, s, stream, pdl) : launch_group_cfg<2, 128>(grp, tiles, 1, s, stream, pdl);
+    return bn == 32 ? launch_group_cfg<1, 32>(grp, tiles, 1, s, stream, pdl) : launch_group_cfg<1, 128>(grp, tiles, 1, s, stream, pdl);
 }
 
 }  // namespace b200
@@ -581,7 +503,20 @@ extern "C" int b200_linear_f16(int M, int N, int K, const void* A, long lda, con
                                const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,
                                void* stream) {
     return b200::linear_f16_launch(M, N, K, A, lda, W, ldw, out, ldo, bias, residual, epilogue, workspace, workspace_bytes,
-                                   static_cast<cudaStream_t>(stream));
+                                   static_cast<cudaStream_t>(stream), /*pdl=*/false);
+}
+
+extern "C" int b200_linear_group_f16(int n, const b200_linear_desc* problems, int M, void* workspace, long workspace_bytes,
+                                     void* stream) {
+    if (n < 0 || M < 0 || (n > 0 && !problems)) return B200_ERR_BAD_ARG;
+    static_assert(sizeof(b200_linear_desc) == sizeof(b200::LinearDesc), "descriptor layouts must match");
+    for (int i = 0; i < n; i++) {
+        const int e = problems[i].epilogue;
+        if (e < B200_EPI_NONE || e > B200_EPI_RESADD || (e == B200_EPI_RESADD && !problems[i].residual)) return B200_ERR_BAD_ARG;
+        if (problems[i].N <= 0 || problems[i].K <= 0) return B200_ERR_BAD_ARG;
+    }
+    return b200::linear_group_launch(n, reinterpret_cast<const b200::LinearDesc*>(problems), M, workspace, workspace_bytes,
+                                     static_cast<cudaStream_t>(stream), /*pdl=*/false);
 }
 
 // Debug aid (not part of the public header): point the GEMM timeline probes at a device buffer of >= 8 * n_ctas uint64.

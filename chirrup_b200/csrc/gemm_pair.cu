@@ -1,0 +1,493 @@
+// Decode-sized dense linear layers on CTA PAIRS:  out (M,N) = epilogue( A (M,K) . W (N,K)^T )  for 128 < M, fp16 in, fp32 in TMEM.
+//
+// Same reference call sites as gemm.cu (/root/reference/Albatross/rwkv7.py:625-630, :637, :649, :678-679, :551).  What differs
+// is the mapping to the machine.  At M = 256 one output tile needs every token row, so the per-SM cost of a K-step is the
+// bytes that enter the SM's shared memory (measured ceiling ~100 GB/s per SM).  Two SMs of a TPC therefore share each tile with
+// tcgen05.mma.cta_group::2 (UMMA 256 x BN x 16): CTA r of the pair loads token rows [128r, 128r+128) of A and rows
+// [r BN/2, (r+1) BN/2) of the W tile, the leader CTA issues the MMAs for both, and each CTA ends up with the 128 x BN fp32
+// accumulator of its own token rows in its own TMEM — half the shared-memory fill per SM of a one-CTA tile of the same shape,
+// twice the CTAs per tile, so that far less K-splitting is needed to occupy the chip.
+//
+//   warp 0 (one lane)   TMA producer: its CTA's A rows and W-half rows per 64-wide K block, completion on the LEADER's mbarrier
+//   warp 1 (one lane)   leader only: tcgen05.mma issuer; tcgen05.commit multicast frees the stage in both CTAs
+//   warps 2-5           epilogue: tcgen05.ld -> fp32 staging in shared memory -> coalesced bias / activation / residual -> fp16
+//
+// One launch carries up to PAIR_MAX_GROUP independent problems that share M (r,k,v and the four LoRA down-projections of a
+// layer are one launch), each with its own tile width BN (multiple of 32, <= 256).  K may additionally be split over the z
+// dimension of the cluster (cluster = 2 x 1 x S): every CTA parks its fp32 partial in an L2-resident workspace in a
+// thread-major layout (coalesced 512-byte warp stores straight from the TMEM registers), the cluster barrier orders the
+// writes, and each CTA then pulls the S partials of its 1/S share of the tile's columns back with bulk copies (all in flight
+// at once) and finishes them in split order: deterministic, no atomics.
+//
+// Programmatic dependent launch: the weight tiles of the first pipeline stages are requested BEFORE griddepcontrol.wait —
+// they do not depend on the preceding kernel — so the weight stream starts under the previous kernel's tail.
+#include <cstdlib>
+
+#include "common.cuh"
+#include "gemm_common.cuh"
+#include "glue.h"
+#include "tmap.h"
+
+namespace b200 {
+namespace {
+
+constexpr int PAIR_THREADS = 192;
+constexpr int PAIR_MAX_GROUP = 8;
+constexpr int PAIR_STAGE_BYTES = 32 * 1024;       // A half 128 x 64 fp16 (16 KiB) + W half up to 128 x 64 fp16 (16 KiB)
+constexpr int PAIR_MAX_STAGES = 6;
+constexpr int PAIR_MAX_SPLIT = 4;                 // cluster = 2 x 1 x S <= 8 CTAs (portable size)
+constexpr int PAIR_UNIT_FLOATS = 128 * 32;        // one parked unit: 128 rows x 32 columns fp32 = 16 KiB, thread-major
+constexpr int PAIR_STAGING_BYTES = 4 * 2 * 32 * STG_LD * 4;  // two 32 x 32(+4) fp32 buffers per epilogue warp = 36 KiB
+constexpr uint32_t PAIR_TMEM_COLS = 256;
+
+struct PairProblem {
+    CUtensorMap tmA;  // box 128 rows x 64
+    CUtensorMap tmW;  // box bn/2 rows x 64
+    GemmArgs g;
+    int tile_end;     // one past this problem's last tile index along blockIdx.x / 2
+    int bn;           // tile width: multiple of 32, <= 256
+};
+
+struct alignas(64) PairGroup {
+    PairProblem p[PAIR_MAX_GROUP];
+    int n;
+    int n_stages;
+};
+
+DEVI uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+DEVI uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+DEVI void cluster_arrive_wait() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// 2-D tiled load whose completion bytes are signalled on an mbarrier given as a shared::cluster address (the pair leader's).
+DEVI void tma_load_2d_pair(void* dst, const CUtensorMap* m, int c0, int c1, uint32_t bar_cluster_addr, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%2, "
+        "%3}], [%4], %5;" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(bar_cluster_addr), "l"(policy)
+        : "memory");
+}
+DEVI void umma_f16_ss_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// Arrive (count 1) on the mbarrier at this shared-memory offset in every CTA of `cta_mask` once all MMAs issued so far are done.
+DEVI void umma_commit_pair(uint64_t* bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                     smem_u32(bar)),
+                 "h"(cta_mask)
+                 : "memory");
+}
+DEVI void tmem_alloc_pair(uint32_t* smem_dst, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+DEVI void tmem_dealloc_pair(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// global -> shared linear bulk copy, completion on a local mbarrier
+DEVI void bulk_load(void* sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(sdst)),
+                 "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+DEVI unsigned long long gtime_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define PPROBE(slot)                                                                                              \
+    do {                                                                                                          \
+        if (g.dbg && (threadIdx.x == 64 || ((slot) == 2 && threadIdx.x == 32)))                                   \
+            g.dbg[((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + (slot)] = gtime_ns(); \
+    } while (0)
+
+// One staged 32-row x 32-column fp32 unit of this warp -> epilogue -> fp16 global, coalesced (lane = 4 columns, 4 rows / instr).
+DEVI void finish_unit(const float* stg, const GemmArgs& g, int row0, int col0, int lane) {
+    const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int r = i * 4 + sub_r;
+        const float4 t = *reinterpret_cast<const float4*>(stg + r * STG_LD + sub_c);
+        const int row = row0 + r, col = col0 + sub_c;
+        if (row < g.M && col < g.N)
+            finish4_rt(g.epi, t, g.out + (size_t)row * g.ldo, g.bias, g.residual ? g.residual + (size_t)row * g.ldo : nullptr, col);
+    }
+}
+
+__global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid_constant__ PairGroup grp) {
+    extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int n_stages = grp.n_stages;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + PAIR_MAX_STAGES * PAIR_STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + PAIR_MAX_STAGES;
+    uint64_t* accum_bar = empty_bar + PAIR_MAX_STAGES;
+    uint64_t* red_bar = accum_bar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(red_bar + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t crank = cluster_ctarank();
+    const int pr = crank & 1;  // rank inside the CTA pair: 0 = leader (issues the MMAs)
+    const int tile = blockIdx.x >> 1;
+    int pi = 0;
+    while (pi + 1 < grp.n && tile >= grp.p[pi].tile_end) pi++;
+    const PairProblem& P = grp.p[pi];
+    const GemmArgs& g = P.g;
+    const int bn = P.bn;
+    const int local_tile = tile - (pi ? grp.p[pi - 1].tile_end : 0);
+    const int n0 = local_tile * bn;
+    const int m0 = blockIdx.y * 256 + pr * 128;
+    const int split = blockIdx.z;
+    const int S = g.n_split;
+    const int kb_total = (g.K + BK - 1) / BK;
+    const int kb0 = split * g.kb_per_split;
+    const int n_kb = min(kb_total, kb0 + g.kb_per_split) - kb0;  // >= 1 by construction of the launch
+    const int n_units = bn >> 5;
+    const uint32_t w_half_bytes = (uint32_t)(bn >> 1) * BK * 2;
+    PPROBE(0);
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&P.tmA);
+        tma_prefetch_desc(&P.tmW);
+        for (int s = 0; s < n_stages; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(accum_bar, 1);
+        mbar_init(red_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_slot, PAIR_TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    cluster_arrive_wait();  // the peer's barriers exist before anything is signalled across the pair
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    PPROBE(1);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            const uint64_t pol_w = policy_evict_first();
+            const uint64_t pol_a = policy_evict_last();
+            const uint32_t tx = 2u * (128u * BK * 2u + w_half_bytes);  // both CTAs' bytes land on the leader's barrier
+            const uint32_t leader = crank & ~1u;
+            const int npre = min(n_kb, n_stages);
+            // weights first: they do not depend on the previous kernel
+            for (int it = 0; it < npre; it++) {
+                uint8_t* st = smem + it * PAIR_STAGE_BYTES;
+                if (pr == 0) mbar_arrive_expect_tx(&full_bar[it], tx);
+                tma_load_2d_pair(st + 128 * BK * 2, &P.tmW, (kb0 + it) * BK, n0 + pr * (bn >> 1),
+                                 mapa_shared(smem_u32(&full_bar[it]), leader), pol_w);
+            }
+            pdl_wait();
+            for (int it = 0; it < npre; it++)
+                tma_load_2d_pair(smem + it * PAIR_STAGE_BYTES, &P.tmA, (kb0 + it) * BK, m0,
+                                 mapa_shared(smem_u32(&full_bar[it]), leader), pol_a);
+            for (int it = npre; it < n_kb; it++) {
+                const int s = it % n_stages;
+                const uint32_t ph = (it / n_stages) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                uint8_t* st = smem + s * PAIR_STAGE_BYTES;
+                if (pr == 0) mbar_arrive_expect_tx(&full_bar[s], tx);
+                const uint32_t bar = mapa_shared(smem_u32(&full_bar[s]), leader);
+                tma_load_2d_pair(st, &P.tmA, (kb0 + it) * BK, m0, bar, pol_a);
+                tma_load_2d_pair(st + 128 * BK * 2, &P.tmW, (kb0 + it) * BK, n0 + pr * (bn >> 1), bar, pol_w);
+            }
+        } else {
+            pdl_wait();
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        pdl_wait();
+        if (pr == 0 && lane == 0) {
+            const uint32_t idesc = umma_idesc_f16(256, (uint32_t)bn);
+            const uint16_t mask = (uint16_t)(3u << (crank & ~1u));
+            for (int it = 0; it < n_kb; it++) {
+                const int s = it % n_stages;
+                const uint32_t ph = (it / n_stages) & 1;
+                mbar_wait(&full_bar[s], ph);
+                if (it == 0) PPROBE(2);
+                tc_fence_after();
+                const uint32_t st = smem_u32(smem + s * PAIR_STAGE_BYTES);
+                const uint64_t adesc = umma_desc_sw128(st);
+                const uint64_t bdesc = umma_desc_sw128(st + 128 * BK * 2);
+#pragma unroll
+                for (int k = 0; k < BK / 16; k++)
+                    umma_f16_ss_pair(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                umma_commit_pair(&empty_bar[s], mask);  // frees the stage in both CTAs once these MMAs have read it
+            }
+            umma_commit_pair(accum_bar, mask);  // accumulators complete (both CTAs)
+        }
+        __syncwarp();
+    } else {
+        pdl_wait();
+        const int q = warp & 3;  // TMEM lane quarter of this warp
+        mbar_wait(accum_bar, 0);
+        PPROBE(3);
+        tc_fence_after();
+        const int row = q * 32 + lane;  // this thread's accumulator row inside the CTA's 128
+        if (S == 1) {
+            float* stg0 = reinterpret_cast<float*>(smem) + q * (2 * 32 * STG_LD);
+#pragma unroll 1
+            for (int u = 0; u < n_units; u++) {
+                if (n0 + u * 32 >= g.N) break;  // columns past N (tail tile)
+                float* stg = stg0 + (u & 1) * (32 * STG_LD);
+                uint32_t v[32];
+                tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + u * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 8; e++)
+                    *reinterpret_cast<float4*>(stg + lane * STG_LD + 4 * e) =
+                        make_float4(__uint_as_float(v[4 * e]), __uint_as_float(v[4 * e + 1]), __uint_as_float(v[4 * e + 2]),
+                                    __uint_as_float(v[4 * e + 3]));
+                __syncwarp();
+                finish_unit(stg, g, m0 + q * 32, n0 + u * 32, lane);
+                // the buffer is reused two units later; the __syncwarp() of the next unit orders this unit's reads before that
+            }
+        } else {
+            // park: unit u of (tile, pair rank, split) = 8 column groups x 128 rows x float4, thread-major
+            float* my_part = g.partials +
+                             ((((size_t)blockIdx.y * (gridDim.x >> 1) + tile) * 2 + pr) * S + split) * (size_t)8 * PAIR_UNIT_FLOATS;
+#pragma unroll 1
+            for (int u = 0; u < n_units; u++) {
+                if (n0 + u * 32 >= g.N) break;
+                uint32_t v[32];
+                tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + u * 32, v);
+                tmem_ld_wait();
+                float4* dst = reinterpret_cast<float4*>(my_part + (size_t)u * PAIR_UNIT_FLOATS) + row;
+#pragma unroll
+                for (int e = 0; e < 8; e++)
+                    __stcg(dst + e * 128, make_float4(__uint_as_float(v[4 * e]), __uint_as_float(v[4 * e + 1]),
+                                                      __uint_as_float(v[4 * e + 2]), __uint_as_float(v[4 * e + 3])));
+            }
+            __threadfence();
+        }
+    }
+
+    if (S > 1) {
+        PPROBE(4);
+        // every CTA of the cluster (both pair ranks, all K splits of this tile) has parked its partial
+        asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy global writes above vs the bulk (async-proxy) reads below
+        cluster_arrive_wait();
+        PPROBE(5);
+        // this CTA finishes units u = split, split + S, ... of its own 128 rows: pull the S partials of each into the (idle)
+        // pipeline stages with bulk copies, all in flight at once
+        const float* base = g.partials + (((size_t)blockIdx.y * (gridDim.x >> 1) + tile) * 2 + pr) * (size_t)S * 8 * PAIR_UNIT_FLOATS;
+        float* land = reinterpret_cast<float*>(smem + PAIR_STAGING_BYTES);  // up to 8 units x 16 KiB
+        int n_mine = 0;
+        for (int u = split; u < n_units && n0 + u * 32 < g.N; u += S) n_mine++;
+        if (threadIdx.x == 64 && n_mine > 0) {
+            asm volatile("fence.proxy.async;" ::: "memory");
+            mbar_arrive_expect_tx(red_bar, (uint32_t)n_mine * S * PAIR_UNIT_FLOATS * 4);
+            int j = 0;
+            for (int u = split; u < n_units && n0 + u * 32 < g.N; u += S, j++)
+                for (int z = 0; z < S; z++)
+                    bulk_load(land + (size_t)(j * S + z) * PAIR_UNIT_FLOATS, base + ((size_t)z * 8 + u) * PAIR_UNIT_FLOATS,
+                              PAIR_UNIT_FLOATS * 4, red_bar);
+        }
+        if (warp >= 2 && n_mine > 0) {
+            const int q = warp & 3;
+            const int row = q * 32 + lane;
+            mbar_wait(red_bar, 0);
+            float* stg0 = reinterpret_cast<float*>(smem) + q * (2 * 32 * STG_LD);
+            int j = 0;
+#pragma unroll 1
+            for (int u = split; u < n_units && n0 + u * 32 < g.N; u += S, j++) {
+                float4 acc[8];
+#pragma unroll
+                for (int e = 0; e < 8; e++) acc[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int z = 0; z < S; z++) {  // fixed order: deterministic sum
+                    const float4* src = reinterpret_cast<const float4*>(land + (size_t)(j * S + z) * PAIR_UNIT_FLOATS) + row;
+#pragma unroll
+                    for (int e = 0; e < 8; e++) {
+                        const float4 t = src[e * 128];
+                        acc[e].x += t.x; acc[e].y += t.y; acc[e].z += t.z; acc[e].w += t.w;
+                    }
+                }
+                float* stg = stg0 + (j & 1) * (32 * STG_LD);
+#pragma unroll
+                for (int e = 0; e < 8; e++) *reinterpret_cast<float4*>(stg + lane * STG_LD + 4 * e) = acc[e];
+                __syncwarp();
+                finish_unit(stg, g, m0 + q * 32, n0 + u * 32, lane);
+            }
+        }
+    }
+
+    PPROBE(6);
+    tc_fence_before();
+    __syncthreads();
+    cluster_arrive_wait();  // neither CTA of a pair may exit (or free TMEM) while the other can still signal / write into it
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, PAIR_TMEM_COLS);
+    }
+}
+
+constexpr int PAIR_SMEM_BYTES = PAIR_MAX_STAGES * PAIR_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+static_assert(PAIR_STAGING_BYTES + 8 * PAIR_UNIT_FLOATS * 4 <= PAIR_MAX_STAGES * PAIR_STAGE_BYTES, "landing zone must fit the stages");
+
+// Pairs of CTAs (clusters of 2 x 1 x s) the device can hold at once.
+int pair_slots(int s) {
+    static int cache[8][PAIR_MAX_SPLIT + 1] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 8) dev = 0;
+    if (cache[dev][s]) return cache[dev][s];
+    cudaFuncSetAttribute(pair_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_BYTES);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2, 1, s);
+    cfg.blockDim = dim3(PAIR_THREADS);
+    cfg.dynamicSmemBytes = PAIR_SMEM_BYTES;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = s;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, pair_gemm_kernel, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = 148 / (2 * s) - (s > 1 ? 2 : 0);  // conservative guess
+    }
+    cache[dev][s] = n;
+    return n;
+}
+
+// Modelled time (us) of one CTA of a (bn, s) plan with kps K-blocks per split (rates: DESIGN.md §3, profiles/r01_gemm_timeline*).
+double pair_cta_cost(int bn, int s, int kps) {
+    const double clk = 1500.0;                                    // MHz under tensor load (power-capped)
+    const double mma = 4.0 * (bn / 2.0);                          // cycles per K block: 4 UMMAs of 256 x bn x 16
+    const double ingest = (16384.0 + bn * 64.0) / 52.0;           // bytes into this SM per K block at ~52 B/clk
+    const double main_us = kps * (mma > ingest ? mma : ingest) / clk;
+    const double epi_us = (s > 1) ? 1.2 + 4.5 * bn / 256.0 : 0.5 + 2.5 * bn / 256.0;
+    return 1.8 + main_us + epi_us;
+}
+
+}  // namespace
+
+// Up to PAIR_MAX_GROUP linear layers that share M (> 128) in ONE launch.  Returns B200_ERR_UNSUPPORTED when the group does
+// not fit this kernel (the caller then uses gemm.cu).
+int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream, bool pdl,
+                      unsigned long long* dbg) {
+    if (n <= 0 || n > PAIR_MAX_GROUP || M <= 128) return B200_ERR_UNSUPPORTED;
+    const int gy = (M + 255) / 256;
+    int min_kb = 1 << 30;
+    for (int i = 0; i < n; i++) {
+        if ((d[i].K & 7) || (d[i].N & 7) || (d[i].lda & 7) || (d[i].ldw & 7) || (d[i].ldo & 7)) return B200_ERR_BAD_ARG;
+        const int kb = (d[i].K + BK - 1) / BK;
+        if (kb < min_kb) min_kb = kb;
+    }
+    // tile widths and the common K split: minimise waves x (time of the slowest CTA)
+    static const bool fixed256 = getenv("B200_PAIR_BN256") != nullptr;
+    int best_s = 1, best_bn[PAIR_MAX_GROUP];
+    double best_cost = 1e30;
+    const int cands[4] = {256, 192, 128, 64};
+    for (int s = 1; s <= PAIR_MAX_SPLIT; s++) {
+        if (s > 1 && (gy > 1 || s > min_kb / 2)) break;
+        bool ok = true;
+        for (int i = 0; i < n && ok; i++) {
+            const int kb = (d[i].K + BK - 1) / BK, kps = (kb + s - 1) / s;
+            if ((kb + kps - 1) / kps != s) ok = false;  // no empty split
+        }
+        if (!ok) continue;
+        const int slots = pair_slots(s);
+        for (int ci = 0; ci < (fixed256 ? 1 : 4); ci++) {
+            int bns[PAIR_MAX_GROUP];
+            long tiles = 0;
+            double worst = 0.0;
+            for (int i = 0; i < n; i++) {
+                int bn = cands[ci];
+                const int n32 = (d[i].N + 31) / 32 * 32;
+                if (bn > n32) bn = n32;
+                bns[i] = bn;
+                tiles += (d[i].N + bn - 1) / bn;
+                const int kb = (d[i].K + BK - 1) / BK;
+                const double c = pair_cta_cost(bn, s, (kb + s - 1) / s);
+                if (c > worst) worst = c;
+            }
+            tiles *= gy;
+            const long waves = (tiles + slots - 1) / slots;
+            const double cost = waves * worst;
+            if (cost < best_cost) {
+                best_cost = cost;
+                best_s = s;
+                for (int i = 0; i < n; i++) best_bn[i] = bns[i];
+            }
+        }
+    }
+    const int s = best_s;
+    PairGroup grp;
+    grp.n = n;
+    grp.n_stages = PAIR_MAX_STAGES;
+    int end = 0;
+    for (int i = 0; i < n; i++) {
+        const int bn = best_bn[i];
+        PairProblem& P = grp.p[i];
+        int rc = make_tmap_2d_f16(&P.tmA, d[i].A, (uint64_t)M, (uint64_t)d[i].K, (uint64_t)d[i].lda * 2, 128, BK,
+                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+        if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+        rc = make_tmap_2d_f16(&P.tmW, d[i].W, (uint64_t)d[i].N, (uint64_t)d[i].K, (uint64_t)d[i].ldw * 2, bn / 2, BK,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+        if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+        GemmArgs& g = P.g;
+        g.M = M; g.N = d[i].N; g.K = d[i].K;
+        g.out = static_cast<__half*>(d[i].out);
+        g.ldo = d[i].ldo;
+        g.bias = static_cast<const __half*>(d[i].bias);
+        g.residual = static_cast<const __half*>(d[i].residual);
+        g.epi = d[i].epi;
+        if (g.epi < B200_EPI_NONE || g.epi > B200_EPI_RESADD || (g.epi == B200_EPI_RESADD && !g.residual)) return B200_ERR_BAD_ARG;
+        g.partials = static_cast<float*>(workspace);
+        const int kb = (d[i].K + BK - 1) / BK;
+        g.kb_per_split = (kb + s - 1) / s;
+        g.n_split = s;
+        g.dbg = dbg;
+        end += (d[i].N + bn - 1) / bn;
+        P.tile_end = end;
+        P.bn = bn;
+    }
+    for (int i = n; i < PAIR_MAX_GROUP; i++) {
+        grp.p[i].tile_end = end;
+        grp.p[i].bn = 32;
+    }
+    if (s > 1) {
+        const long need = (long)end * gy * 2 * s * 8 * PAIR_UNIT_FLOATS * 4;
+        if (workspace == nullptr || workspace_bytes < need) return B200_ERR_WORKSPACE;
+    }
+    cudaError_t e = cudaFuncSetAttribute(pair_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * end, gy, s);
+    cfg.blockDim = dim3(PAIR_THREADS);
+    cfg.dynamicSmemBytes = PAIR_SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = s;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 2 : 1;
+    return (int)cudaLaunchKernelEx(&cfg, pair_gemm_kernel, grp);
+}
+
+}  // namespace b200

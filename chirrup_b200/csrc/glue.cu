@@ -80,6 +80,8 @@ DEVI H8 layer_norm8(const H8& x, bool active, int C, const __half* w, const __ha
 
 __global__ void embed_gather_kernel(int M, int C, const int* __restrict__ tokens, const __half* __restrict__ emb,
                                     __half* __restrict__ x) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int m = blockIdx.x;
     const __half* src = emb + (size_t)tokens[m] * C;
     __half* dst = x + (size_t)m * C;
@@ -95,6 +97,8 @@ __global__ void __launch_bounds__(1024) ln_shift_mix_kernel(int T, int C, const 
                                                             const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
                                                             __half* __restrict__ shift, long shift_stride,
                                                             const int* __restrict__ slot_idx, MixPtrs<NMIX> mp) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float red[33];
     const int m = blockIdx.x;
     const int b = m / T, t = m - b * T;
@@ -138,6 +142,8 @@ __global__ void __launch_bounds__(1024) ln_shift_mix_kernel(int T, int C, const 
 __global__ void __launch_bounds__(1024) ln_rows_kernel(int C, const __half* __restrict__ x, long row_step, long row_off,
                                                        const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
                                                        __half* __restrict__ out) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float red[33];
     const int c0 = threadIdx.x * 8;
     const bool active = c0 < C;
@@ -149,6 +155,8 @@ __global__ void __launch_bounds__(1024) ln_rows_kernel(int C, const __half* __re
 }
 
 __global__ void add_elapsed_kernel(int B, int T, int* __restrict__ elapsed) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < B) elapsed[i] += T;
 }
@@ -158,6 +166,8 @@ DEVI void st2(__half* p, float x, float y) { *reinterpret_cast<__half2*>(p) = __
 
 // One warp per (token m, head h); lane holds channels h*64 + 2*lane, +1.                         rwkv7.py:632-637
 __global__ void __launch_bounds__(128) tmix_prep_kernel(TmixPrepArgs p) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int H = p.C >> 6;
     const int gw = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (gw >= p.M * H) return;
@@ -184,6 +194,8 @@ __global__ void __launch_bounds__(128) tmix_prep_kernel(TmixPrepArgs p) {
 
 // One warp per (token, head): GroupNorm over the head's 64 outputs, bonus term, gate.               rwkv7.py:647-649
 __global__ void __launch_bounds__(128) tmix_post_kernel(TmixPostArgs p) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int H = p.C >> 6;
     const int gw = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (gw >= p.M * H) return;
@@ -208,6 +220,8 @@ __global__ void __launch_bounds__(128) tmix_post_kernel(TmixPostArgs p) {
 // the worker's top_k == 1 / temperature == 0 path, chirrup/utils/samplers.py:171-255).  One CTA per row.
 __global__ void __launch_bounds__(256) argmax_rows_kernel(int V, const __half* __restrict__ logits, long ld,
                                                           int* __restrict__ out) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float sv[8];
     __shared__ int si[8];
     const __half* row = logits + (size_t)blockIdx.x * ld;
@@ -244,50 +258,45 @@ int ln_threads(int C) {
 
 }  // namespace
 
-int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __half* x, cudaStream_t s) {
+int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __half* x, cudaStream_t s, bool pdl) {
     if (M <= 0) return 0;
-    embed_gather_kernel<<<M, 128, 0, s>>>(M, C, tokens, emb, x);
-    return (int)cudaGetLastError();
+    return launch_kernel(embed_gather_kernel, dim3(M), dim3(128), 0, s, pdl, 0, M, C, tokens, emb, x);
 }
 int launch_ln_shift_mix6(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
-                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s) {
+                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl) {
     if (B * T <= 0) return 0;
-    ln_shift_mix_kernel<6><<<B * T, ln_threads(C), 0, s>>>(T, C, x, ln_w, ln_b, shift, shift_stride, slot_idx, mp);
-    return (int)cudaGetLastError();
+    return launch_kernel(ln_shift_mix_kernel<6>, dim3(B * T), dim3(ln_threads(C)), 0, s, pdl, 0, T, C, x, ln_w, ln_b, shift,
+                         shift_stride, slot_idx, mp);
 }
 int launch_ln_shift_mix1(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
-                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s) {
+                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s, bool pdl) {
     if (B * T <= 0) return 0;
-    ln_shift_mix_kernel<1><<<B * T, ln_threads(C), 0, s>>>(T, C, x, ln_w, ln_b, shift, shift_stride, slot_idx, mp);
-    return (int)cudaGetLastError();
+    return launch_kernel(ln_shift_mix_kernel<1>, dim3(B * T), dim3(ln_threads(C)), 0, s, pdl, 0, T, C, x, ln_w, ln_b, shift,
+                         shift_stride, slot_idx, mp);
 }
 int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off, const __half* ln_w, const __half* ln_b,
-                   __half* out, cudaStream_t s) {
+                   __half* out, cudaStream_t s, bool pdl) {
     if (rows <= 0) return 0;
-    ln_rows_kernel<<<rows, ln_threads(C), 0, s>>>(C, x, row_step, row_off, ln_w, ln_b, out);
-    return (int)cudaGetLastError();
+    return launch_kernel(ln_rows_kernel, dim3(rows), dim3(ln_threads(C)), 0, s, pdl, 0, C, x, row_step, row_off, ln_w, ln_b, out);
 }
-int launch_add_elapsed(int B, int T, int* elapsed, cudaStream_t s) {
+int launch_add_elapsed(int B, int T, int* elapsed, cudaStream_t s, bool pdl) {
     if (B <= 0) return 0;
-    add_elapsed_kernel<<<(B + 127) / 128, 128, 0, s>>>(B, T, elapsed);
-    return (int)cudaGetLastError();
+    return launch_kernel(add_elapsed_kernel, dim3((B + 127) / 128), dim3(128), 0, s, pdl, 0, B, T, elapsed);
 }
 int launch_argmax_rows(int rows, int V, const __half* logits, long ld, int* out, cudaStream_t s) {
     if (rows <= 0) return 0;
     argmax_rows_kernel<<<rows, 256, 0, s>>>(V, logits, ld, out);
     return (int)cudaGetLastError();
 }
-int launch_tmix_prep(const TmixPrepArgs& a, cudaStream_t s) {
+int launch_tmix_prep(const TmixPrepArgs& a, cudaStream_t s, bool pdl) {
     const int warps = a.M * (a.C >> 6);
     if (warps <= 0) return 0;
-    tmix_prep_kernel<<<(warps + 3) / 4, 128, 0, s>>>(a);
-    return (int)cudaGetLastError();
+    return launch_kernel(tmix_prep_kernel, dim3((warps + 3) / 4), dim3(128), 0, s, pdl, 0, a);
 }
-int launch_tmix_post(const TmixPostArgs& a, cudaStream_t s) {
+int launch_tmix_post(const TmixPostArgs& a, cudaStream_t s, bool pdl) {
     const int warps = a.M * (a.C >> 6);
     if (warps <= 0) return 0;
-    tmix_post_kernel<<<(warps + 3) / 4, 128, 0, s>>>(a);
-    return (int)cudaGetLastError();
+    return launch_kernel(tmix_post_kernel, dim3((warps + 3) / 4), dim3(128), 0, s, pdl, 0, a);
 }
 
 }  // namespace b200

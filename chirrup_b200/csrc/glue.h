@@ -12,14 +12,14 @@ struct MixPtrs {
     __half* out[NMIX];        // outputs (M, C)
 };
 
-int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __half* x, cudaStream_t s);
+int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __half* x, cudaStream_t s, bool pdl = false);
 int launch_ln_shift_mix6(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
-                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s);
+                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl = false);
 int launch_ln_shift_mix1(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
-                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s);
+                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s, bool pdl = false);
 int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off, const __half* ln_w, const __half* ln_b,
-                   __half* out, cudaStream_t s);
-int launch_add_elapsed(int B, int T, int* elapsed, cudaStream_t s);
+                   __half* out, cudaStream_t s, bool pdl = false);
+int launch_add_elapsed(int B, int T, int* elapsed, cudaStream_t s, bool pdl = false);
 int launch_argmax_rows(int rows, int V, const __half* logits, long ld, int* out, cudaStream_t s);
 
 struct TmixPrepArgs {
@@ -28,7 +28,7 @@ struct TmixPrepArgs {
     const __half *k_k, *k_a;
     __half *k_out, *v_out, *a_out, *b_out;
 };
-int launch_tmix_prep(const TmixPrepArgs& a, cudaStream_t s);
+int launch_tmix_prep(const TmixPrepArgs& a, cudaStream_t s, bool pdl = false);
 
 struct TmixPostArgs {
     int M, C;
@@ -36,7 +36,7 @@ struct TmixPostArgs {
     const __half *ln_w, *ln_b, *r_k;
     __half* out;
 };
-int launch_tmix_post(const TmixPostArgs& a, cudaStream_t s);
+int launch_tmix_post(const TmixPostArgs& a, cudaStream_t s, bool pdl = false);
 
 // wkv7.cu: fused TMix core (prep + WKV-7 + GroupNorm/bonus/gate), inputs (B*T, C) fp16
 struct WkvFusedArgs {
@@ -47,12 +47,16 @@ struct WkvFusedArgs {
     const int* elapsed_t;
     const int* slot_idx;
 };
-int launch_wkv7_fused(const WkvFusedArgs& a, void* state, long state_slot_stride, int n_slots, cudaStream_t stream);
+int launch_wkv7_fused(const WkvFusedArgs& a, void* state, long state_slot_stride, int n_slots, cudaStream_t stream,
+                      bool pdl = false);
+int launch_wkv7_seq(int B, int T, int C, int H, void* state, long state_slot_stride, int n_slots, const void* r, const void* w,
+                    const void* k, const void* v, const void* a, const void* b, void* y, const int* elapsed_t,
+                    const int* slot_idx, cudaStream_t stream, bool pdl = false);
 
 // gemm.cu
 int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* W, long ldw, void* out, long ldo,
                       const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,
-                      cudaStream_t stream);
+                      cudaStream_t stream, bool pdl = false);
 
 struct LinearDesc {
     int N, K;
@@ -67,6 +71,12 @@ struct LinearDesc {
     int epi;
 };
 // Up to four linear layers sharing M in one launch (gemm.cu); larger groups / M fall back to one launch each.
-int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream);
+int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream,
+                        bool pdl = false);
+
+// gemm_pair.cu: the same, on cta_group::2 CTA pairs (128 < M; up to 8 problems).  Returns B200_ERR_UNSUPPORTED when the group
+// does not fit that kernel.
+int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream, bool pdl,
+                      unsigned long long* dbg = nullptr);
 
 }  // namespace b200

@@ -105,6 +105,10 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
     int n = 0, rc = 0;
     static const bool debug_sync = getenv("B200_DEBUG_SYNC") != nullptr;
     const bool unfused_tmix = getenv("B200_UNFUSED_TMIX") != nullptr;  // A/B switch: the three-kernel chain of glue.cu
+    // Programmatic dependent launch for every kernel after the first (the first one orders the step after whatever the caller
+    // enqueued before it); every kernel of the step calls griddepcontrol.wait before touching its predecessors' outputs.
+    const bool pdl = getenv("B200_NO_PDL") == nullptr;
+    const bool no_group = getenv("B200_NO_PAIR") != nullptr;  // A/B switch: the one-CTA-per-tile GEMM path of gemm.cu
 #define RUN(call)                                                                                     \
     do {                                                                                              \
         rc = (call);                                                                                  \
@@ -117,12 +121,13 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
     } while (0)
     auto lin = [&](long rows, int N, int K, const __half* A, const __half* W, __half* out, const __half* bias,
                    const __half* res, int epi) {
-        return linear_f16_launch((int)rows, N, K, A, K, W, K, out, N, bias, res, epi, ws.counters_and_partials, ws.lin_bytes, st);
+        return linear_f16_launch((int)rows, N, K, A, K, W, K, out, N, bias, res, epi, ws.counters_and_partials, ws.lin_bytes, st,
+                                 pdl);
     };
     __half* s0 = static_cast<__half*>(state0);
     __half* s1 = static_cast<__half*>(state1);
 
-    RUN(launch_embed_gather((int)M, C, tokens, m->gw[0], ws.x, st));
+    RUN(launch_embed_gather((int)M, C, tokens, m->gw[0], ws.x, st, /*pdl=*/false));
     for (int l = 0; l < L; l++) {
         const __half** w = m->lw + (size_t)l * B200_LW_COUNT;
         // ---- TMix
@@ -132,27 +137,35 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             mp.out[i] = ws.mix[i];
         }
         __half *xr = ws.mix[0], *xw = ws.mix[1], *xk = ws.mix[2], *xv = ws.mix[3], *xa = ws.mix[4], *xg = ws.mix[5];
-        RUN(launch_ln_shift_mix6(B, T, C, ws.x, w[B200_LW_LN1_W], w[B200_LW_LN1_B], s0 + l * s0_layer_stride, C, slot_idx, mp, st));
+        RUN(launch_ln_shift_mix6(B, T, C, ws.x, w[B200_LW_LN1_W], w[B200_LW_LN1_B], s0 + l * s0_layer_stride, C, slot_idx, mp, st, pdl));
         __half* vbuf = (l == 0) ? ws.vfirst : ws.v;  // layer 0: v_first = v (rwkv7.py:636)
-        RUN(lin(M, C, C, xr, w[B200_LW_RECEPTANCE], ws.r, nullptr, nullptr, B200_EPI_NONE));
-        RUN(lin(M, C, C, xk, w[B200_LW_KEY], ws.k, nullptr, nullptr, B200_EPI_NONE));
-        RUN(lin(M, C, C, xv, w[B200_LW_VALUE], vbuf, nullptr, nullptr, B200_EPI_NONE));
-        // the four LoRA down-projections in one grouped launch, then the four up-projections in another
-        // (w: tanh, +w0 ; a: +a0, sigmoid ; g: sigmoid inside ; v-gate: +v0, sigmoid — rwkv7.py:626, :629, :630, :637)
+        // r, k, v and the four LoRA down-projections read only the six mixes: ONE grouped launch (7 problems; 6 on layer 0, which
+        // has no v-gate, rwkv7.py:636), then the four up-projections in another
+        // (w: tanh, +w0 ; a: +a0, sigmoid ; g: sigmoid inside ; v-gate: +v0, sigmoid — rwkv7.py:625-630, :637)
         {
             const int nl = (l > 0) ? 4 : 3;
-            LinearDesc dn[4] = {
+            LinearDesc dn[7] = {
+                {C, C, xr, C, w[B200_LW_RECEPTANCE], C, ws.r, C, nullptr, nullptr, B200_EPI_NONE},
+                {C, C, xk, C, w[B200_LW_KEY], C, ws.k, C, nullptr, nullptr, B200_EPI_NONE},
+                {C, C, xv, C, w[B200_LW_VALUE], C, vbuf, C, nullptr, nullptr, B200_EPI_NONE},
                 {m->d_w, C, xw, C, w[B200_LW_W1], C, ws.lora[0], m->d_w, nullptr, nullptr, B200_EPI_TANH},
                 {m->d_a, C, xa, C, w[B200_LW_A1], C, ws.lora[1], m->d_a, nullptr, nullptr, B200_EPI_NONE},
                 {m->d_g, C, xg, C, w[B200_LW_G1], C, ws.lora[2], m->d_g, nullptr, nullptr, B200_EPI_SIGMOID},
                 {m->d_v, C, xv, C, w[B200_LW_V1], C, ws.lora[3], m->d_v, nullptr, nullptr, B200_EPI_NONE}};
-            RUN(linear_group_launch(nl, dn, (int)M, ws.counters_and_partials, ws.lin_bytes, st));
+            if (M > 128 && !no_group) {
+                RUN(linear_group_launch(3 + nl, dn, (int)M, ws.counters_and_partials, ws.lin_bytes, st, pdl));
+            } else {
+                for (int i = 0; i < 3; i++)
+                    RUN(linear_f16_launch((int)M, dn[i].N, dn[i].K, dn[i].A, dn[i].lda, dn[i].W, dn[i].ldw, dn[i].out, dn[i].ldo,
+                                          nullptr, nullptr, dn[i].epi, ws.counters_and_partials, ws.lin_bytes, st, pdl));
+                RUN(linear_group_launch(nl, dn + 3, (int)M, ws.counters_and_partials, ws.lin_bytes, st, pdl));
+            }
             LinearDesc up[4] = {
                 {C, m->d_w, ws.lora[0], m->d_w, w[B200_LW_W2], m->d_w, ws.w, C, w[B200_LW_W0], nullptr, B200_EPI_NONE},
                 {C, m->d_a, ws.lora[1], m->d_a, w[B200_LW_A2], m->d_a, ws.a, C, w[B200_LW_A0], nullptr, B200_EPI_SIGMOID},
                 {C, m->d_g, ws.lora[2], m->d_g, w[B200_LW_G2], m->d_g, ws.g, C, nullptr, nullptr, B200_EPI_NONE},
                 {C, m->d_v, ws.lora[3], m->d_v, w[B200_LW_V2], m->d_v, ws.vg, C, w[B200_LW_V0], nullptr, B200_EPI_SIGMOID}};
-            RUN(linear_group_launch(nl, up, (int)M, ws.counters_and_partials, ws.lin_bytes, st));
+            RUN(linear_group_launch(nl, up, (int)M, ws.counters_and_partials, ws.lin_bytes, st, pdl));
         }
         if (!unfused_tmix) {
             // prep + WKV-7 + GroupNorm/bonus/gate in one kernel per (sequence, head) tile
@@ -164,7 +177,7 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             fa.k_k = w[B200_LW_K_K]; fa.k_a = w[B200_LW_K_A]; fa.r_k = w[B200_LW_R_K];
             fa.ln_w = w[B200_LW_LNX_W]; fa.ln_b = w[B200_LW_LNX_B];
             fa.out = ws.yg; fa.elapsed_t = elapsed; fa.slot_idx = slot_idx;
-            RUN(launch_wkv7_fused(fa, s1 + l * s1_layer_stride, (long)C * 64, n_slots, st));
+            RUN(launch_wkv7_fused(fa, s1 + l * s1_layer_stride, (long)C * 64, n_slots, st, pdl));
         } else {
             TmixPrepArgs pa;
             pa.M = (int)M; pa.C = C;
@@ -173,16 +186,16 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             pa.v_first = l > 0 ? ws.vfirst : nullptr;
             pa.k_k = w[B200_LW_K_K]; pa.k_a = w[B200_LW_K_A];
             pa.k_out = ws.k2; pa.v_out = ws.v2; pa.a_out = ws.an; pa.b_out = ws.bn;
-            RUN(launch_tmix_prep(pa, st));
+            RUN(launch_tmix_prep(pa, st, pdl));
             const __half* vv = l > 0 ? ws.v2 : ws.vfirst;
-            RUN(b200_wkv7_forward_seq(B, T, C, H, s1 + l * s1_layer_stride, (long)C * 64, n_slots, ws.r, ws.w, ws.k2, vv, ws.an,
-                                      ws.bn, ws.y, elapsed, slot_idx, st));
+            RUN(launch_wkv7_seq(B, T, C, H, s1 + l * s1_layer_stride, (long)C * 64, n_slots, ws.r, ws.w, ws.k2, vv, ws.an, ws.bn,
+                                ws.y, elapsed, slot_idx, st, pdl));
             TmixPostArgs po;
             po.M = (int)M; po.C = C;
             po.y = ws.y; po.r = ws.r; po.k = ws.k2; po.v = vv; po.g = ws.g;
             po.ln_w = w[B200_LW_LNX_W]; po.ln_b = w[B200_LW_LNX_B]; po.r_k = w[B200_LW_R_K];
             po.out = ws.yg;
-            RUN(launch_tmix_post(po, st));
+            RUN(launch_tmix_post(po, st, pdl));
         }
         RUN(lin(M, C, C, ws.yg, w[B200_LW_OUTPUT], ws.x, nullptr, ws.x, B200_EPI_RESADD));
         // ---- CMix
@@ -190,20 +203,20 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
         mc.mix[0] = w[B200_LW_FFN_X_K];
         mc.out[0] = ws.kx;
         RUN(launch_ln_shift_mix1(B, T, C, ws.x, w[B200_LW_LN2_W], w[B200_LW_LN2_B], s0 + l * s0_layer_stride + s0_which_stride, C,
-                                 slot_idx, mc, st));
+                                 slot_idx, mc, st, pdl));
         RUN(lin(M, F, C, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, nullptr, nullptr, B200_EPI_RELU_SQ));
         RUN(lin(M, C, F, ws.hidden, w[B200_LW_FFN_VALUE], ws.x, nullptr, ws.x, B200_EPI_RESADD));
     }
     if (logits) {
         if (full_output) {
-            RUN(launch_ln_rows((int)M, C, ws.x, 1, 0, m->gw[1], m->gw[2], ws.xo, st));
+            RUN(launch_ln_rows((int)M, C, ws.x, 1, 0, m->gw[1], m->gw[2], ws.xo, st, pdl));
             RUN(lin(M, m->V, C, ws.xo, m->gw[3], static_cast<__half*>(logits), nullptr, nullptr, B200_EPI_NONE));
         } else {
-            RUN(launch_ln_rows(B, C, ws.x, T, T - 1, m->gw[1], m->gw[2], ws.xo, st));
+            RUN(launch_ln_rows(B, C, ws.x, T, T - 1, m->gw[1], m->gw[2], ws.xo, st, pdl));
             RUN(lin(B, m->V, C, ws.xo, m->gw[3], static_cast<__half*>(logits), nullptr, nullptr, B200_EPI_NONE));
         }
     }
-    RUN(launch_add_elapsed(B, T, elapsed, st));
+    RUN(launch_add_elapsed(B, T, elapsed, st, pdl));
 #undef RUN
     m->last_launches = n;
     return 0;

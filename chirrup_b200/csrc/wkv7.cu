@@ -45,6 +45,7 @@ __global__ void __launch_bounds__(HS) wkv7_seq_kernel(const __grid_constant__ CU
     __shared__ __align__(16) __half sv[5][HS];  // w~, k, a, b, r of the current token
     __shared__ __align__(8) uint64_t bar;
 
+    pdl_launch_dependents();
     const int bb = blockIdx.x / H;
     const int h = blockIdx.x - bb * H;
     const int i = threadIdx.x;
@@ -57,12 +58,15 @@ __global__ void __launch_bounds__(HS) wkv7_seq_kernel(const __grid_constant__ CU
     }
     __syncthreads();
     if (i == 0) {
+        // the state tile (like slot_idx / elapsed_t) is not produced by the preceding kernels of the step: under PDL its load
+        // starts while they are still draining
         mbar_arrive_expect_tx(&bar, HS * HS * 2);
         tma_load_2d(tile, &tm_state, 0, row0, &bar);
     }
 
     const int t0 = elapsed_t[bb];
     size_t idx = (size_t)bb * T * C + (size_t)h * HS + i;
+    pdl_wait();
     TokenRegs cur;
     cur.r = r_[idx]; cur.w = w_[idx]; cur.k = k_[idx]; cur.v = v_[idx]; cur.a = a_[idx]; cur.b = b_[idx];
 
@@ -188,6 +192,7 @@ __global__ void __launch_bounds__(HS, 12) wkv7_fused_kernel(const __grid_constan
     __shared__ float red[4][2];
     __shared__ __align__(8) uint64_t bar;
 
+    pdl_launch_dependents();
     const int T = p.T, C = p.C, H = p.H;
     const int bb = blockIdx.x / H;
     const int h = blockIdx.x - bb * H;
@@ -210,6 +215,8 @@ __global__ void __launch_bounds__(HS, 12) wkv7_fused_kernel(const __grid_constan
     const float kk_w = __half2float(p.k_k[c]), ka_w = __half2float(p.k_a[c]), rk_w = __half2float(p.r_k[c]);
     const float ln_w = __half2float(p.ln_w[c]), ln_b = __half2float(p.ln_b[c]);
     size_t idx = (size_t)bb * T * C + c;
+    // PDL: the state-tile load and the per-channel weights above do not depend on the preceding kernels; r..g below do
+    pdl_wait();
     FusedIn cur;
     fused_load(cur, p, idx);
 
@@ -336,7 +343,7 @@ int wkv7_make_state_tmap(CUtensorMap* tm, const void* state, int n_slots, int H,
     return make_tmap_2d_f16(tm, state, rows, HS, HS * 2, HS, HS, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
 }
 
-int launch_wkv7_fused(const WkvFusedArgs& a, void* state, long state_slot_stride, int n_slots, cudaStream_t stream) {
+int launch_wkv7_fused(const WkvFusedArgs& a, void* state, long state_slot_stride, int n_slots, cudaStream_t stream, bool pdl) {
     if (a.B <= 0 || a.T <= 0) return 0;
     if (a.H * HS != a.C) return B200_ERR_BAD_ARG;
     CUtensorMap tm;
@@ -344,17 +351,17 @@ int launch_wkv7_fused(const WkvFusedArgs& a, void* state, long state_slot_stride
     if (rc) return rc;
     WkvFusedArgs p = a;
     p.rows_per_slot = (int)(state_slot_stride / HS);
-    wkv7_fused_kernel<<<a.B * a.H, HS, 0, stream>>>(tm, p);
-    return (int)cudaGetLastError();
+    return launch_kernel(wkv7_fused_kernel, dim3(a.B * a.H), dim3(HS), 0, stream, pdl, 0, tm, p);
 }
 
 }  // namespace b200
 
 using namespace b200;
 
-extern "C" int b200_wkv7_forward_seq(int B, int T, int C, int H, void* state, long state_slot_stride, int n_slots,
-                                     const void* r, const void* w, const void* k, const void* v, const void* a,
-                                     const void* b, void* y, const int* elapsed_t, const int* slot_idx, void* stream) {
+namespace b200 {
+int launch_wkv7_seq(int B, int T, int C, int H, void* state, long state_slot_stride, int n_slots, const void* r, const void* w,
+                    const void* k, const void* v, const void* a, const void* b, void* y, const int* elapsed_t,
+                    const int* slot_idx, cudaStream_t stream, bool pdl) {
     if (B < 0 || T < 0 || H <= 0 || H * HS != C) return B200_ERR_BAD_ARG;  // reference: assert(H*_N_ == C), .cu:314
     if (B == 0 || T == 0) return 0;
     if (!slot_idx) n_slots = B;
@@ -362,11 +369,18 @@ extern "C" int b200_wkv7_forward_seq(int B, int T, int C, int H, void* state, lo
     CUtensorMap tm;
     int rc = wkv7_make_state_tmap(&tm, state, n_slots, H, state_slot_stride);
     if (rc) return rc;
-    wkv7_seq_kernel<<<B * H, HS, 0, static_cast<cudaStream_t>(stream)>>>(
-        tm, T, C, H, (int)(state_slot_stride / HS), static_cast<const __half*>(r), static_cast<const __half*>(w),
-        static_cast<const __half*>(k), static_cast<const __half*>(v), static_cast<const __half*>(a),
-        static_cast<const __half*>(b), static_cast<__half*>(y), elapsed_t, slot_idx);
-    return (int)cudaGetLastError();
+    return launch_kernel(wkv7_seq_kernel, dim3(B * H), dim3(HS), 0, stream, pdl, 0, tm, T, C, H, (int)(state_slot_stride / HS),
+                         static_cast<const __half*>(r), static_cast<const __half*>(w), static_cast<const __half*>(k),
+                         static_cast<const __half*>(v), static_cast<const __half*>(a), static_cast<const __half*>(b),
+                         static_cast<__half*>(y), elapsed_t, slot_idx);
+}
+}  // namespace b200
+
+extern "C" int b200_wkv7_forward_seq(int B, int T, int C, int H, void* state, long state_slot_stride, int n_slots,
+                                     const void* r, const void* w, const void* k, const void* v, const void* a,
+                                     const void* b, void* y, const int* elapsed_t, const int* slot_idx, void* stream) {
+    return b200::launch_wkv7_seq(B, T, C, H, state, state_slot_stride, n_slots, r, w, k, v, a, b, y, elapsed_t, slot_idx,
+                                 static_cast<cudaStream_t>(stream), false);
 }
 
 extern "C" int b200_wkv7_forward_one(int B, int C, int H, void* state, long state_slot_stride, int n_slots, const void* r,

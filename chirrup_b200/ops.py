@@ -4,6 +4,7 @@ plus the dense linear op.  torch is used for device memory and the current strea
 """
 from __future__ import annotations
 
+import ctypes
 from typing import Optional
 
 import torch
@@ -146,3 +147,35 @@ def tmix_core_fused(state, r, w, k, v, a, g, vgate, v_first, k_k, k_a, r_k, ln_w
                                          elapsed_t.data_ptr(), p(slot_idx), _stream(r))
     _lib.check(rc, "b200_tmix_core_fused")
     return out
+
+
+def linear_group(xs, Ws, biases=None, epilogues=None, residuals=None, outs=None):
+    """Several ``F.linear`` calls that share the number of rows M in ONE launch (``b200_linear_group_f16``): ``xs[i]`` (M, K_i),
+    ``Ws[i]`` (N_i, K_i) -> list of (M, N_i).  Mirrors the r/k/v + LoRA-down group of one TMix layer (``Albatross/rwkv7.py:625-630``)."""
+    n = len(xs)
+    biases = biases or [None] * n
+    epilogues = epilogues or [EPI_NONE] * n
+    residuals = residuals or [None] * n
+    M = xs[0].shape[0]
+    descs = (_lib.LinearDesc * n)()
+    keep = []
+    res = []
+    for i in range(n):
+        x, W = xs[i], Ws[i]
+        _req(x, "x")
+        _req(W, "W")
+        if x.dim() != 2 or x.shape[0] != M or x.stride(1) != 1 or W.stride(1) != 1:
+            raise ValueError("linear_group: every x must be (M, K) with unit inner stride, every W K-major")
+        out = outs[i] if outs is not None else torch.empty((M, W.shape[0]), dtype=torch.float16, device=x.device)
+        res.append(out)
+        keep.append((x, W, out))
+        d = descs[i]
+        d.N, d.K = W.shape[0], x.shape[1]
+        d.A, d.lda, d.W, d.ldw, d.out, d.ldo = x.data_ptr(), x.stride(0), W.data_ptr(), W.stride(0), out.data_ptr(), out.stride(0)
+        d.bias = biases[i].data_ptr() if biases[i] is not None else None
+        d.residual = residuals[i].data_ptr() if residuals[i] is not None else None
+        d.epilogue = epilogues[i]
+    ws = _workspace(xs[0].device, M, max(W.shape[0] for W in Ws))
+    rc = _lib.lib().b200_linear_group_f16(n, ctypes.cast(descs, ctypes.c_void_p), M, ws.data_ptr(), ws.numel(), _stream(xs[0]))
+    _lib.check(rc, "b200_linear_group_f16")
+    return res

@@ -92,6 +92,26 @@ int b200_linear_f16(int M, int N, int K, const void* A, long lda, const void* W,
                     void* stream);
 long b200_linear_workspace_bytes(int max_M, int max_N);
 
+/*
+ * Up to 8 independent linear layers that share M in ONE launch (e.g. the r, k, v projections and the four LoRA
+ * down-projections of a TMix layer, Albatross/rwkv7.py:625-630, :637 — they all read the six token-shift mixes).
+ * `problems` is a HOST array of n descriptors; fields as in b200_linear_f16.  For 128 < M each output tile is computed by a
+ * CTA pair (tcgen05.mma.cta_group::2); other M, or more than 8 problems, run as one launch per problem.
+ */
+typedef struct b200_linear_desc {
+    int N, K;
+    const void* A;
+    long lda;
+    const void* W;
+    long ldw;
+    void* out;
+    long ldo;
+    const void* bias;
+    const void* residual;
+    int epilogue;
+} b200_linear_desc;
+int b200_linear_group_f16(int n, const b200_linear_desc* problems, int M, void* workspace, long workspace_bytes, void* stream);
+
 /* out[i,:] = LayerNorm(x[i,:]) * w + b over `rows` contiguous rows of C fp16 (eps 1e-5, fp32 statistics); used at load time
  * to fold ln0 into the embedding table (Albatross/rwkv7.py:206).  out may alias x. */
 int b200_layer_norm_f16(int rows, int C, const void* x, const void* w, const void* b, void* out, void* stream);

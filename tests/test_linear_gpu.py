@@ -60,6 +60,52 @@ def test_linear_epilogues(epi, M, N, K):
     assert torch.allclose(y.float(), ref.float(), rtol=3e-3, atol=3e-3), (y.float() - ref.float()).abs().max().item()
 
 
+@pytest.mark.parametrize("M", [256, 200, 129, 512, 64])
+def test_linear_group_tmix_shapes(M):
+    """The grouped launch of one TMix layer (r, k, v + the four LoRA down-projections: 7 problems, mixed N and epilogues) and of
+    the four up-projections (K = 96..480), each against the fp32 reference; M > 128 runs on CTA pairs (cta_group::2)."""
+    from chirrup_b200 import ops
+
+    C = 1024
+    g = torch.Generator(device="cuda").manual_seed(M)
+    rn = lambda *s: torch.randn(*s, generator=g, device="cuda")
+    dims = [(C, ops.EPI_NONE), (C, ops.EPI_NONE), (C, ops.EPI_NONE), (128, ops.EPI_TANH), (128, ops.EPI_NONE),
+            (480, ops.EPI_SIGMOID), (96, ops.EPI_NONE)]
+    xs = [rn(M, C).half() for _ in dims]
+    Ws = [(rn(N, C) * C ** -0.5).half() for N, _ in dims]
+    ys = ops.linear_group(xs, Ws, epilogues=[e for _, e in dims])
+    torch.cuda.synchronize()
+    for x, W, (N, e), y in zip(xs, Ws, dims, ys):
+        ref = _ref(x, W, None, e, None)
+        assert torch.allclose(y.float(), ref.float(), rtol=3e-3, atol=3e-3), (N, e, (y.float() - ref.float()).abs().max().item())
+    ups = [(128, ops.EPI_NONE, True), (128, ops.EPI_SIGMOID, True), (480, ops.EPI_NONE, False), (96, ops.EPI_SIGMOID, True)]
+    xs = [rn(M, K).half() for K, _, _ in ups]
+    Ws = [(rn(C, K) * K ** -0.5).half() for K, _, _ in ups]
+    bs = [rn(C).half() if b else None for _, _, b in ups]
+    ys = ops.linear_group(xs, Ws, biases=bs, epilogues=[e for _, e, _ in ups])
+    torch.cuda.synchronize()
+    for x, W, b, (K, e, _), y in zip(xs, Ws, bs, ups, ys):
+        ref = _ref(x, W, b, e, None)
+        assert torch.allclose(y.float(), ref.float(), rtol=3e-3, atol=3e-3), (K, e, (y.float() - ref.float()).abs().max().item())
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 4096, 16384), (256, 512, 512), (255, 264, 4096), (1024, 1024, 1024)])
+def test_linear_pair_splitk_and_tails(M, N, K):
+    """CTA-pair kernel: K split over the cluster (deterministic thread-major partials), N / M tails, several M blocks."""
+    from chirrup_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(N + K)
+    x = torch.randn(M, K, generator=g, device="cuda").half()
+    W = (torch.randn(N, K, generator=g, device="cuda") * K ** -0.5).half()
+    res = torch.randn(M, N, generator=g, device="cuda").half()
+    a = ops.linear(x, W, None, ops.EPI_RESADD, res)
+    b = ops.linear(x, W, None, ops.EPI_RESADD, res)
+    torch.cuda.synchronize()
+    ref = _ref(x, W, None, ops.EPI_RESADD, res)
+    assert torch.equal(a, b)
+    assert torch.allclose(a.float(), ref.float(), rtol=3e-3, atol=3e-3), (a.float() - ref.float()).abs().max().item()
+
+
 def test_linear_inplace_residual_and_determinism():
     from chirrup_b200 import ops
 
