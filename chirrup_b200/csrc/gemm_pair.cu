@@ -116,18 +116,128 @@ DEVI unsigned long long gtime_ns() {
             g.dbg[((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + (slot)] = gtime_ns(); \
     } while (0)
 
-// One staged 32-row x 32-column fp32 unit of this warp -> epilogue -> fp16 global, coalesced (lane = 4 columns, 4 rows / instr).
-DEVI void finish_unit(const float* stg, const GemmArgs& g, int row0, int col0, int lane) {
-    const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;
+// ---- epilogue helpers.  Everything the inner loops need is hoisted into registers (EpiCtx) and the epilogue kind is a template
+// parameter chosen once per CTA: the first version re-read the problem block with indexed constant loads and ran a 5-way switch
+// per 4 outputs (~70 instructions per 4 outputs, ncu source page profiles/r01_pair_ffnkey_ncu_v5.txt), which made the
+// epilogue as long as 40 % of the main loop.
+struct EpiCtx {
+    __half* out;
+    const __half* bias;
+    const __half* residual;
+    long ldo;
+    int M, N;
+};
+DEVI void sts128(uint32_t addr, float x, float y, float z, float w) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+DEVI float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+DEVI void tmem_ld_unit(uint32_t tmem_base, int q, int u, float (&v)[32]) {
+    uint32_t (&w)[32] = reinterpret_cast<uint32_t (&)[32]>(v);
+    tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + u * 32, w);
+}
+
+// Eight consecutive outputs of one row: fp32 -> epilogue -> 8 x fp16 (one 16-byte store for the caller).
+template <int EPI>
+DEVI uint4 finish8(const float4 lo, const float4 hi, const uint4 b8, const uint4 r8) {
+    const float a[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    const __half2* bp = reinterpret_cast<const __half2*>(&b8);
+    const __half2* rp = reinterpret_cast<const __half2*>(&r8);
+    uint4 o;
+    __half2* op = reinterpret_cast<__half2*>(&o);
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
-        const int r = i * 4 + sub_r;
-        const float4 t = *reinterpret_cast<const float4*>(stg + r * STG_LD + sub_c);
-        const int row = row0 + r, col = col0 + sub_c;
-        if (row < g.M && col < g.N)
-            finish4_rt(g.epi, t, g.out + (size_t)row * g.ldo, g.bias, g.residual ? g.residual + (size_t)row * g.ldo : nullptr, col);
+    for (int e = 0; e < 4; e++) {
+        const float2 bv = __half22float2(bp[e]), rv = __half22float2(rp[e]);
+        op[e] = __floats2half2_rn(epilogue_op<EPI>(a[2 * e], bv.x, rv.x), epilogue_op<EPI>(a[2 * e + 1], bv.y, rv.y));
+    }
+    return o;
+}
+
+// One 32-row x 32-column unit of this warp.  In: thread = row (lane), v = its 32 consecutive columns.  The unit is transposed
+// through a padded shared-memory buffer so that a warp store covers 8 rows x 64 contiguous bytes (lane = row i*8 + lane/4,
+// 8 columns), bias / residual are fetched as 16-byte vectors BEFORE the staging so their latency hides under it.
+template <int EPI>
+DEVI void emit_unit(const float (&v)[32], uint32_t stg, const EpiCtx& c, int row0, int col0, int lane) {
+    const int sub_r = lane >> 2, c8 = (lane & 3) * 8;
+    const int col = col0 + c8;
+    const bool col_ok = col < c.N;
+    uint4 b8 = make_uint4(0u, 0u, 0u, 0u);
+    uint4 r8[4];
+    if ((EPI == B200_EPI_NONE || EPI == B200_EPI_TANH || EPI == B200_EPI_SIGMOID) && c.bias != nullptr && col_ok)
+        b8 = *reinterpret_cast<const uint4*>(c.bias + col);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        r8[i] = make_uint4(0u, 0u, 0u, 0u);
+        if (EPI == B200_EPI_RESADD) {
+            const int row = row0 + i * 8 + sub_r;
+            if (row < c.M && col_ok) r8[i] = *reinterpret_cast<const uint4*>(c.residual + (size_t)row * c.ldo + col);
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; e++) sts128(stg + (uint32_t)(lane * STG_LD + 4 * e) * 4u, v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int r = i * 8 + sub_r;
+        const uint32_t a = stg + (uint32_t)(r * STG_LD + c8) * 4u;
+        const float4 lo = lds128(a), hi = lds128(a + 16u);
+        const int row = row0 + r;
+        if (row < c.M && col_ok) *reinterpret_cast<uint4*>(c.out + (size_t)row * c.ldo + col) = finish8<EPI>(lo, hi, b8, r8[i]);
     }
 }
+
+// No K split: drain this warp's 32 accumulator rows unit by unit (the TMEM load of unit u+1 is in flight while unit u is emitted).
+template <int EPI>
+DEVI void epilogue_direct(uint32_t tmem_base, int q, int lane, int n_valid, const EpiCtx& c, int row0, int n0, uint32_t stg0) {
+    float va[32], vb[32];
+    tmem_ld_unit(tmem_base, q, 0, va);
+#pragma unroll 1
+    for (int u = 0; u < n_valid; u += 2) {
+        tmem_ld_wait();
+        if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
+        emit_unit<EPI>(va, stg0, c, row0, n0 + u * 32, lane);
+        if (u + 1 < n_valid) {
+            tmem_ld_wait();
+            if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
+            emit_unit<EPI>(vb, stg0 + 32 * STG_LD * 4, c, row0, n0 + (u + 1) * 32, lane);
+        }
+    }
+}
+
+// K split: sum the S landed partials of each of this CTA's units in split order, then emit.
+template <int EPI>
+DEVI void epilogue_reduce(uint32_t land, int S, int split, int n_valid, int row, int lane, const EpiCtx& c, int row0, int n0,
+                          uint32_t stg0) {
+    int j = 0;
+#pragma unroll 1
+    for (int u = split; u < n_valid; u += S, j++) {
+        float acc[32];
+#pragma unroll
+        for (int e = 0; e < 32; e++) acc[e] = 0.f;
+#pragma unroll 1
+        for (int z = 0; z < S; z++) {  // fixed order: deterministic sum
+            const uint32_t src = land + (uint32_t)((j * S + z) * PAIR_UNIT_FLOATS * 4 + row * 16);
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+                const float4 t = lds128(src + (uint32_t)e * 128u * 16u);
+                acc[4 * e] += t.x; acc[4 * e + 1] += t.y; acc[4 * e + 2] += t.z; acc[4 * e + 3] += t.w;
+            }
+        }
+        emit_unit<EPI>(acc, stg0 + (uint32_t)(j & 1) * (32 * STG_LD * 4), c, row0, n0 + u * 32, lane);
+    }
+}
+
+#define EPI_DISPATCH(epi, CALL)                                       \
+    switch (epi) {                                                    \
+        case B200_EPI_NONE: { constexpr int E = B200_EPI_NONE; CALL; } break;       \
+        case B200_EPI_TANH: { constexpr int E = B200_EPI_TANH; CALL; } break;       \
+        case B200_EPI_SIGMOID: { constexpr int E = B200_EPI_SIGMOID; CALL; } break; \
+        case B200_EPI_RELU_SQ: { constexpr int E = B200_EPI_RELU_SQ; CALL; } break; \
+        default: { constexpr int E = B200_EPI_RESADD; CALL; } break;                \
+    }
 
 __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid_constant__ PairGroup grp) {
     extern __shared__ uint8_t smem_raw[];
@@ -159,6 +269,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
     const int kb0 = split * g.kb_per_split;
     const int n_kb = min(kb_total, kb0 + g.kb_per_split) - kb0;  // >= 1 by construction of the launch
     const int n_units = bn >> 5;
+    int n_valid = (g.N - n0 + 31) >> 5;  // units of this tile that hold columns < N (tail tile of a problem)
+    if (n_valid > n_units) n_valid = n_units;
+    const int epi = g.epi;
+    EpiCtx ec;
+    ec.out = g.out; ec.bias = g.bias; ec.residual = g.residual; ec.ldo = g.ldo; ec.M = g.M; ec.N = g.N;
     const uint32_t w_half_bytes = (uint32_t)(bn >> 1) * BK * 2;
     PPROBE(0);
 
@@ -242,39 +357,30 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
         PPROBE(3);
         tc_fence_after();
         const int row = q * 32 + lane;  // this thread's accumulator row inside the CTA's 128
+        const uint32_t stg0 = smem_u32(smem) + (uint32_t)q * (2 * 32 * STG_LD * 4);
         if (S == 1) {
-            float* stg0 = reinterpret_cast<float*>(smem) + q * (2 * 32 * STG_LD);
-#pragma unroll 1
-            for (int u = 0; u < n_units; u++) {
-                if (n0 + u * 32 >= g.N) break;  // columns past N (tail tile)
-                float* stg = stg0 + (u & 1) * (32 * STG_LD);
-                uint32_t v[32];
-                tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + u * 32, v);
-                tmem_ld_wait();
-#pragma unroll
-                for (int e = 0; e < 8; e++)
-                    *reinterpret_cast<float4*>(stg + lane * STG_LD + 4 * e) =
-                        make_float4(__uint_as_float(v[4 * e]), __uint_as_float(v[4 * e + 1]), __uint_as_float(v[4 * e + 2]),
-                                    __uint_as_float(v[4 * e + 3]));
-                __syncwarp();
-                finish_unit(stg, g, m0 + q * 32, n0 + u * 32, lane);
-                // the buffer is reused two units later; the __syncwarp() of the next unit orders this unit's reads before that
-            }
+            EPI_DISPATCH(epi, epilogue_direct<E>(tmem_base, q, lane, n_valid, ec, m0 + q * 32, n0, stg0));
         } else {
-            // park: unit u of (tile, pair rank, split) = 8 column groups x 128 rows x float4, thread-major
-            float* my_part = g.partials +
-                             ((((size_t)blockIdx.y * (gridDim.x >> 1) + tile) * 2 + pr) * S + split) * (size_t)8 * PAIR_UNIT_FLOATS;
+            // park: unit u of (tile, pair rank, split) = 8 column groups x 128 rows x float4, thread-major; the TMEM load of
+            // unit u+1 is in flight while unit u is stored
+            float4* my_part = reinterpret_cast<float4*>(
+                g.partials + ((((size_t)blockIdx.y * (gridDim.x >> 1) + tile) * 2 + pr) * S + split) * (size_t)8 * PAIR_UNIT_FLOATS) + row;
+            float va[32], vb[32];
+            tmem_ld_unit(tmem_base, q, 0, va);
 #pragma unroll 1
-            for (int u = 0; u < n_units; u++) {
-                if (n0 + u * 32 >= g.N) break;
-                uint32_t v[32];
-                tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + u * 32, v);
+            for (int u = 0; u < n_valid; u += 2) {
                 tmem_ld_wait();
-                float4* dst = reinterpret_cast<float4*>(my_part + (size_t)u * PAIR_UNIT_FLOATS) + row;
+                if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
+                float4* dst = my_part + (size_t)u * (PAIR_UNIT_FLOATS / 4);
 #pragma unroll
-                for (int e = 0; e < 8; e++)
-                    __stcg(dst + e * 128, make_float4(__uint_as_float(v[4 * e]), __uint_as_float(v[4 * e + 1]),
-                                                      __uint_as_float(v[4 * e + 2]), __uint_as_float(v[4 * e + 3])));
+                for (int e = 0; e < 8; e++) __stcg(dst + e * 128, make_float4(va[4 * e], va[4 * e + 1], va[4 * e + 2], va[4 * e + 3]));
+                if (u + 1 < n_valid) {
+                    tmem_ld_wait();
+                    if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
+                    dst += PAIR_UNIT_FLOATS / 4;
+#pragma unroll
+                    for (int e = 0; e < 8; e++) __stcg(dst + e * 128, make_float4(vb[4 * e], vb[4 * e + 1], vb[4 * e + 2], vb[4 * e + 3]));
+                }
             }
             __threadfence();
         }
@@ -291,41 +397,21 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
         const float* base = g.partials + (((size_t)blockIdx.y * (gridDim.x >> 1) + tile) * 2 + pr) * (size_t)S * 8 * PAIR_UNIT_FLOATS;
         float* land = reinterpret_cast<float*>(smem + PAIR_STAGING_BYTES);  // up to 8 units x 16 KiB
         int n_mine = 0;
-        for (int u = split; u < n_units && n0 + u * 32 < g.N; u += S) n_mine++;
+        for (int u = split; u < n_valid; u += S) n_mine++;
         if (threadIdx.x == 64 && n_mine > 0) {
             asm volatile("fence.proxy.async;" ::: "memory");
             mbar_arrive_expect_tx(red_bar, (uint32_t)n_mine * S * PAIR_UNIT_FLOATS * 4);
             int j = 0;
-            for (int u = split; u < n_units && n0 + u * 32 < g.N; u += S, j++)
+            for (int u = split; u < n_valid; u += S, j++)
                 for (int z = 0; z < S; z++)
                     bulk_load(land + (size_t)(j * S + z) * PAIR_UNIT_FLOATS, base + ((size_t)z * 8 + u) * PAIR_UNIT_FLOATS,
                               PAIR_UNIT_FLOATS * 4, red_bar);
         }
         if (warp >= 2 && n_mine > 0) {
             const int q = warp & 3;
-            const int row = q * 32 + lane;
             mbar_wait(red_bar, 0);
-            float* stg0 = reinterpret_cast<float*>(smem) + q * (2 * 32 * STG_LD);
-            int j = 0;
-#pragma unroll 1
-            for (int u = split; u < n_units && n0 + u * 32 < g.N; u += S, j++) {
-                float4 acc[8];
-#pragma unroll
-                for (int e = 0; e < 8; e++) acc[e] = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int z = 0; z < S; z++) {  // fixed order: deterministic sum
-                    const float4* src = reinterpret_cast<const float4*>(land + (size_t)(j * S + z) * PAIR_UNIT_FLOATS) + row;
-#pragma unroll
-                    for (int e = 0; e < 8; e++) {
-                        const float4 t = src[e * 128];
-                        acc[e].x += t.x; acc[e].y += t.y; acc[e].z += t.z; acc[e].w += t.w;
-                    }
-                }
-                float* stg = stg0 + (j & 1) * (32 * STG_LD);
-#pragma unroll
-                for (int e = 0; e < 8; e++) *reinterpret_cast<float4*>(stg + lane * STG_LD + 4 * e) = acc[e];
-                __syncwarp();
-                finish_unit(stg, g, m0 + q * 32, n0 + u * 32, lane);
-            }
+            EPI_DISPATCH(epi, epilogue_reduce<E>(smem_u32(land), S, split, n_valid, q * 32 + lane, lane, ec, m0 + q * 32, n0,
+                                                 smem_u32(smem) + (uint32_t)q * (2 * 32 * STG_LD * 4)));
         }
     }
 
@@ -391,6 +477,9 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
     int min_kb = 1 << 30;
     for (int i = 0; i < n; i++) {
         if ((d[i].K & 7) || (d[i].N & 7) || (d[i].lda & 7) || (d[i].ldw & 7) || (d[i].ldo & 7)) return B200_ERR_BAD_ARG;
+        // the epilogue moves 8 fp16 (16 bytes) per access
+        if ((reinterpret_cast<uintptr_t>(d[i].out) | reinterpret_cast<uintptr_t>(d[i].bias) | reinterpret_cast<uintptr_t>(d[i].residual)) & 15)
+            return B200_ERR_UNSUPPORTED;
         const int kb = (d[i].K + BK - 1) / BK;
         if (kb < min_kb) min_kb = kb;
     }
