@@ -82,6 +82,9 @@ DEVI void gemm_body(const CUtensorMap* tmAp, const CUtensorMap* tmWp, const Gemm
     const int kb1 = min(kb_total, kb0 + g.kb_per_split);
     const int n_kb = kb1 - kb0;  // >= 1 by construction of the launch
     const bool splitk = g.n_split > 1;
+    const int epi = g.epi;
+    EpiCtx ec;
+    ec.out = g.out; ec.bias = g.bias; ec.residual = g.residual; ec.ldo = g.ldo; ec.M = g.M; ec.N = g.N;
     pdl_launch_dependents();
     PROBE(0);
 
@@ -149,97 +152,69 @@ DEVI void gemm_body(const CUtensorMap* tmAp, const CUtensorMap* tmWp, const Gemm
         }
         __syncwarp();
     } else {
-        // ---- epilogue warps, phase 1: drain TMEM.  tcgen05.ld gives thread = row; a per-warp shared-memory transpose (the
-        // pipeline stages are idle by now) turns that into lane = 4 consecutive columns so that every global access is coalesced.
+        // ---- epilogue warps: drain TMEM.  tcgen05.ld gives thread = row.  Without a K split each 32 x 32 unit goes through
+        // emit_unit (gemm_common.cuh: per-warp shared-memory transpose -> coalesced 16-byte stores with the fused epilogue);
+        // with a K split the unit is parked in the L2-resident workspace in thread-major order (512 contiguous bytes per warp
+        // store, straight from the registers).
         mbar_wait(accum_bar, 0);
         PROBE(3);
         tc_fence_after();
-        // two staging buffers per warp in the (now idle) pipeline stages
-        float* stg0 = reinterpret_cast<float*>(smem) + q * (2 * 32 * STG_LD);
+        const uint32_t stg0 = smem_u32(smem) + (uint32_t)q * (2 * 32 * STG_LD * 4);  // two staging buffers per warp (idle stages)
+        const int row = q * 32 + lane;
         float* my_part = splitk ? g.partials + ((size_t)tile_id * g.n_split + split) * (size_t)C::kUnits * UNIT_FLOATS : nullptr;
-        const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;
-        int n_parked = 0;
+        int cnt = 0;
 #pragma unroll 1
         for (int u = 0; u < C::kUnits; u++) {
             const int mt = u / (BN / 32), c = u - mt * (BN / 32);
             if (n0 + c * 32 >= g.N) continue;  // columns past N (N tail of the last tile)
-            float* stg = stg0 + (n_parked & 1) * (32 * STG_LD);
-            if (splitk && n_parked >= 2) {  // the bulk store that last used this buffer must have read it
-                if (lane == 0) tma_store_wait_read<1>();
-                __syncwarp();
-            }
-            uint32_t v[32];
-            tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + mt * BN + c * 32, v);
+            float v[32];
+            tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + mt * BN + c * 32,
+                               reinterpret_cast<uint32_t (&)[32]>(v));
             tmem_ld_wait();
-#pragma unroll
-            for (int e = 0; e < 8; e++)
-                *reinterpret_cast<float4*>(stg + lane * STG_LD + 4 * e) =
-                    make_float4(__uint_as_float(v[4 * e]), __uint_as_float(v[4 * e + 1]), __uint_as_float(v[4 * e + 2]),
-                                __uint_as_float(v[4 * e + 3]));
             if (splitk) {
-                // park this warp's 32 rows of the unit (one contiguous 4.5 KiB slab) with a TMA bulk store
-                fence_proxy_async();
-                __syncwarp();
-                if (lane == 0) {
-                    bulk_store(my_part + (size_t)u * UNIT_FLOATS + (size_t)q * 32 * STG_LD, stg, 32 * STG_LD * 4);
-                    tma_store_commit();
-                }
-                n_parked++;
-            } else {
-                __syncwarp();
+                float4* dst = reinterpret_cast<float4*>(my_part + (size_t)u * UNIT_FLOATS) + row;
 #pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    const int r = i * 4 + sub_r;  // row inside this warp's 32
-                    const float4 t = *reinterpret_cast<const float4*>(stg + r * STG_LD + sub_c);
-                    const int row = m0 + mt * 128 + q * 32 + r, col = n0 + c * 32 + sub_c;
-                    if (row < g.M && col < g.N)
-                        finish4_rt(g.epi, t, g.out + (size_t)row * g.ldo, g.bias,
-                                   g.residual ? g.residual + (size_t)row * g.ldo : nullptr, col);
-                }
-                __syncwarp();
+                for (int e = 0; e < 8; e++) __stcg(dst + e * 128, make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]));
+            } else {
+                EPI_DISPATCH(epi, emit_unit<E>(v, stg0 + (uint32_t)(cnt & 1) * (32 * STG_LD * 4), ec, m0 + mt * 128 + q * 32,
+                                               n0 + c * 32, lane));
+                cnt++;
             }
         }
-        if (splitk && lane == 0) {
-            tma_store_wait<0>();  // all parked slabs are written
-            asm volatile("fence.proxy.async;" ::: "memory");
-        }
-        __syncwarp();
+        if (splitk) __threadfence();
     }
 
     if (splitk) {
         // every CTA of the cluster (= every K split of this tile) has parked its partial: release/acquire at cluster scope
         PROBE(4);
-        __threadfence();
         cluster_sync_all();
         PROBE(5);
         if (warp >= 2) {
             const float* base = g.partials + (size_t)tile_id * g.n_split * (size_t)C::kUnits * UNIT_FLOATS;
-            const int sub_r = lane >> 3, sub_c = (lane & 7) * 4;
+            const uint32_t stg0 = smem_u32(smem) + (uint32_t)q * (2 * 32 * STG_LD * 4);
+            const int row = q * 32 + lane;
+            int cnt = 0;
 #pragma unroll 1
             for (int u = split; u < C::kUnits; u += g.n_split) {  // this CTA's share of the tile
                 const int mt = u / (BN / 32), c = u - mt * (BN / 32);
                 if (n0 + c * 32 >= g.N) continue;
-                float4 acc[8];
+                float acc[32];
 #pragma unroll
-                for (int i = 0; i < 8; i++) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
+                for (int e = 0; e < 32; e++) acc[e] = 0.f;
+#pragma unroll 2
                 for (int z = 0; z < g.n_split; z++) {  // fixed order: deterministic sum
-                    const float* src = base + ((size_t)z * C::kUnits + u) * UNIT_FLOATS + (size_t)(q * 32 + sub_r) * STG_LD + sub_c;
+                    const float4* src = reinterpret_cast<const float4*>(base + ((size_t)z * C::kUnits + u) * UNIT_FLOATS) + row;
                     float4 t[8];
 #pragma unroll
-                    for (int i = 0; i < 8; i++) t[i] = __ldcg(reinterpret_cast<const float4*>(src + (size_t)i * 4 * STG_LD));
+                    for (int e = 0; e < 8; e++) t[e] = __ldcg(src + e * 128);
 #pragma unroll
-                    for (int i = 0; i < 8; i++) {
-                        acc[i].x += t[i].x; acc[i].y += t[i].y; acc[i].z += t[i].z; acc[i].w += t[i].w;
+                    for (int e = 0; e < 8; e++) {
+                        acc[4 * e] += t[e].x; acc[4 * e + 1] += t[e].y; acc[4 * e + 2] += t[e].z; acc[4 * e + 3] += t[e].w;
                     }
                 }
-#pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    const int row = m0 + mt * 128 + q * 32 + i * 4 + sub_r, col = n0 + c * 32 + sub_c;
-                    if (row < g.M && col < g.N)
-                        finish4_rt(g.epi, acc[i], g.out + (size_t)row * g.ldo, g.bias,
-                                   g.residual ? g.residual + (size_t)row * g.ldo : nullptr, col);
-                }
+                EPI_DISPATCH(epi, emit_unit<E>(acc, stg0 + (uint32_t)(cnt & 1) * (32 * STG_LD * 4), ec, m0 + mt * 128 + q * 32,
+                                               n0 + c * 32, lane));
+                cnt++;
             }
         }
     }
@@ -377,6 +352,10 @@ int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* 
     if (M < 0 || N <= 0 || K <= 0 || (K & 7) || (N & 7) || (lda & 7) || (ldw & 7) || (ldo & 7)) return B200_ERR_BAD_ARG;
     if (epilogue < B200_EPI_NONE || epilogue > B200_EPI_RESADD) return B200_ERR_BAD_ARG;
     if (epilogue == B200_EPI_RESADD && residual == nullptr) return B200_ERR_BAD_ARG;
+    // TMA needs 16-byte aligned operands; the epilogue moves 8 fp16 per access
+    if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(out) |
+         reinterpret_cast<uintptr_t>(bias) | reinterpret_cast<uintptr_t>(residual)) & 15)
+        return B200_ERR_BAD_ARG;
     if (M == 0) return 0;
     if (M > 128 && !no_pair()) {  // decode / prefill sized token counts: CTA pairs (gemm_pair.cu)
         LinearDesc d1 = {N, K, A, lda, W, ldw, out, ldo, bias, residual, epilogue};
@@ -431,6 +410,9 @@ int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long
     int max_n = 0, min_kb = 1 << 30;
     for (int i = 0; i < n; i++) {
         if ((d[i].K & 7) || (d[i].N & 7) || (d[i].lda & 7) || (d[i].ldw & 7) || (d[i].ldo & 7)) return B200_ERR_BAD_ARG;
+        if ((reinterpret_cast<uintptr_t>(d[i].A) | reinterpret_cast<uintptr_t>(d[i].W) | reinterpret_cast<uintptr_t>(d[i].out) |
+             reinterpret_cast<uintptr_t>(d[i].bias) | reinterpret_cast<uintptr_t>(d[i].residual)) & 15)
+            return B200_ERR_BAD_ARG;
         if (d[i].N > max_n) max_n = d[i].N;
         const int kb = (d[i].K + BK - 1) / BK;
         if (kb < min_kb) min_kb = kb;
@@ -518,6 +500,10 @@ extern "C" int b200_linear_group_f16(int n, const b200_linear_desc* problems, in
     return b200::linear_group_launch(n, reinterpret_cast<const b200::LinearDesc*>(problems), M, workspace, workspace_bytes,
                                      static_cast<cudaStream_t>(stream), /*pdl=*/false);
 }
+
+namespace b200 { int pair_slots_query(int s); }
+// Debug aid (not part of the public header): CTA pairs x K-splits the device can co-schedule (cudaOccupancyMaxActiveClusters).
+extern "C" int b200_debug_pair_slots(int s) { return b200::pair_slots_query(s); }
 
 // Debug aid (not part of the public header): point the GEMM timeline probes at a device buffer of >= 8 * n_ctas uint64.
 extern "C" void b200_debug_gemm_probe(void* buf) { b200::gemm_set_debug_buffer(static_cast<unsigned long long*>(buf)); }

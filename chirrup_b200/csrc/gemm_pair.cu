@@ -116,77 +116,9 @@ DEVI unsigned long long gtime_ns() {
             g.dbg[((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + (slot)] = gtime_ns(); \
     } while (0)
 
-// ---- epilogue helpers.  Everything the inner loops need is hoisted into registers (EpiCtx) and the epilogue kind is a template
-// parameter chosen once per CTA: the first version re-read the problem block with indexed constant loads and ran a 5-way switch
-// per 4 outputs (~70 instructions per 4 outputs, ncu source page profiles/r01_pair_ffnkey_ncu_v5.txt), which made the
-// epilogue as long as 40 % of the main loop.
-struct EpiCtx {
-    __half* out;
-    const __half* bias;
-    const __half* residual;
-    long ldo;
-    int M, N;
-};
-DEVI void sts128(uint32_t addr, float x, float y, float z, float w) {
-    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
-}
-DEVI float4 lds128(uint32_t addr) {
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
-    return v;
-}
 DEVI void tmem_ld_unit(uint32_t tmem_base, int q, int u, float (&v)[32]) {
     uint32_t (&w)[32] = reinterpret_cast<uint32_t (&)[32]>(v);
     tmem_ld_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + u * 32, w);
-}
-
-// Eight consecutive outputs of one row: fp32 -> epilogue -> 8 x fp16 (one 16-byte store for the caller).
-template <int EPI>
-DEVI uint4 finish8(const float4 lo, const float4 hi, const uint4 b8, const uint4 r8) {
-    const float a[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-    const __half2* bp = reinterpret_cast<const __half2*>(&b8);
-    const __half2* rp = reinterpret_cast<const __half2*>(&r8);
-    uint4 o;
-    __half2* op = reinterpret_cast<__half2*>(&o);
-#pragma unroll
-    for (int e = 0; e < 4; e++) {
-        const float2 bv = __half22float2(bp[e]), rv = __half22float2(rp[e]);
-        op[e] = __floats2half2_rn(epilogue_op<EPI>(a[2 * e], bv.x, rv.x), epilogue_op<EPI>(a[2 * e + 1], bv.y, rv.y));
-    }
-    return o;
-}
-
-// One 32-row x 32-column unit of this warp.  In: thread = row (lane), v = its 32 consecutive columns.  The unit is transposed
-// through a padded shared-memory buffer so that a warp store covers 8 rows x 64 contiguous bytes (lane = row i*8 + lane/4,
-// 8 columns), bias / residual are fetched as 16-byte vectors BEFORE the staging so their latency hides under it.
-template <int EPI>
-DEVI void emit_unit(const float (&v)[32], uint32_t stg, const EpiCtx& c, int row0, int col0, int lane) {
-    const int sub_r = lane >> 2, c8 = (lane & 3) * 8;
-    const int col = col0 + c8;
-    const bool col_ok = col < c.N;
-    uint4 b8 = make_uint4(0u, 0u, 0u, 0u);
-    uint4 r8[4];
-    if ((EPI == B200_EPI_NONE || EPI == B200_EPI_TANH || EPI == B200_EPI_SIGMOID) && c.bias != nullptr && col_ok)
-        b8 = *reinterpret_cast<const uint4*>(c.bias + col);
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        r8[i] = make_uint4(0u, 0u, 0u, 0u);
-        if (EPI == B200_EPI_RESADD) {
-            const int row = row0 + i * 8 + sub_r;
-            if (row < c.M && col_ok) r8[i] = *reinterpret_cast<const uint4*>(c.residual + (size_t)row * c.ldo + col);
-        }
-    }
-#pragma unroll
-    for (int e = 0; e < 8; e++) sts128(stg + (uint32_t)(lane * STG_LD + 4 * e) * 4u, v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
-    __syncwarp();
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        const int r = i * 8 + sub_r;
-        const uint32_t a = stg + (uint32_t)(r * STG_LD + c8) * 4u;
-        const float4 lo = lds128(a), hi = lds128(a + 16u);
-        const int row = row0 + r;
-        if (row < c.M && col_ok) *reinterpret_cast<uint4*>(c.out + (size_t)row * c.ldo + col) = finish8<EPI>(lo, hi, b8, r8[i]);
-    }
 }
 
 // No K split: drain this warp's 32 accumulator rows unit by unit (the TMEM load of unit u+1 is in flight while unit u is emitted).
@@ -229,15 +161,6 @@ DEVI void epilogue_reduce(uint32_t land, int S, int split, int n_valid, int row,
         emit_unit<EPI>(acc, stg0 + (uint32_t)(j & 1) * (32 * STG_LD * 4), c, row0, n0 + u * 32, lane);
     }
 }
-
-#define EPI_DISPATCH(epi, CALL)                                       \
-    switch (epi) {                                                    \
-        case B200_EPI_NONE: { constexpr int E = B200_EPI_NONE; CALL; } break;       \
-        case B200_EPI_TANH: { constexpr int E = B200_EPI_TANH; CALL; } break;       \
-        case B200_EPI_SIGMOID: { constexpr int E = B200_EPI_SIGMOID; CALL; } break; \
-        case B200_EPI_RELU_SQ: { constexpr int E = B200_EPI_RELU_SQ; CALL; } break; \
-        default: { constexpr int E = B200_EPI_RESADD; CALL; } break;                \
-    }
 
 __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid_constant__ PairGroup grp) {
     extern __shared__ uint8_t smem_raw[];
@@ -468,6 +391,8 @@ double pair_cta_cost(int bn, int s, int kps) {
 
 }  // namespace
 
+int pair_slots_query(int s) { return (s >= 1 && s <= PAIR_MAX_SPLIT) ? pair_slots(s) : 0; }
+
 // Up to PAIR_MAX_GROUP linear layers that share M (> 128) in ONE launch.  Returns B200_ERR_UNSUPPORTED when the group does
 // not fit this kernel (the caller then uses gemm.cu).
 int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream, bool pdl,
@@ -484,12 +409,15 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
         if (kb < min_kb) min_kb = kb;
     }
     // tile widths and the common K split: minimise waves x (time of the slowest CTA)
-    static const bool fixed256 = getenv("B200_PAIR_BN256") != nullptr;
+    static const int force_bn = getenv("B200_PAIR_BN") ? atoi(getenv("B200_PAIR_BN")) : 0;  // tuning overrides
+    static const int force_s = getenv("B200_PAIR_S") ? atoi(getenv("B200_PAIR_S")) : 0;
+    const bool fixed256 = force_bn != 0;
     int best_s = 1, best_bn[PAIR_MAX_GROUP];
     double best_cost = 1e30;
-    const int cands[4] = {256, 192, 128, 64};
+    const int cands[4] = {force_bn ? force_bn : 256, 192, 128, 64};
     for (int s = 1; s <= PAIR_MAX_SPLIT; s++) {
         if (s > 1 && (gy > 1 || s > min_kb / 2)) break;
+        if (force_s && s != force_s && force_s <= min_kb / 2 && gy == 1) continue;
         bool ok = true;
         for (int i = 0; i < n && ok; i++) {
             const int kb = (d[i].K + BK - 1) / BK, kps = (kb + s - 1) / s;
