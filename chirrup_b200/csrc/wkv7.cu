@@ -7,6 +7,8 @@
 // movement: the 64x64 fp16 state tile is staged global -> shared by one TMA tensor copy with the hardware 128-byte swizzle
 // (conflict-free 128-bit row reads, no software transpose), updated in registers, written back through the same swizzled
 // buffer with one TMA store.  A slot-index vector lets the caller address state rows indirectly (no physical slot swaps).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tmap.h"
 #include "glue.h"
@@ -334,6 +336,138 @@ __global__ void __launch_bounds__(HS, 12) wkv7_fused_kernel(const __grid_constan
     if (i == 0) tma_store_wait_read<0>();  // the tile must stay valid until the bulk store has read it
 }
 
+// Decode form (T = 1) of the fused TMix core: same arithmetic, op for op, as wkv7_fused_kernel, with the token loop, the
+// next-token prefetch and every value that would have to stay live across the WKV chain removed from the registers (the
+// per-thread outputs of the vector prep wait in shared memory), so that 16 CTAs fit on an SM instead of 12: 128 KiB of state
+// loads in flight per SM.  This is the launch the decode step makes 32 times.
+__global__ void __launch_bounds__(HS, 16) wkv7_fused_one_kernel(const __grid_constant__ CUtensorMap tm_state, const WkvFusedArgs p) {
+    __shared__ __align__(1024) uint8_t tile[HS * HS * 2];
+    __shared__ __align__(16) __half sv[5][HS];  // w~, k, a, b, r
+    __shared__ float keep[3][HS];               // v', bonus share, gate of thread i (parked across the WKV chain)
+    __shared__ float red[4][2];
+    __shared__ __align__(8) uint64_t bar;
+
+    pdl_launch_dependents();
+    const int C = p.C, H = p.H;
+    const int bb = blockIdx.x / H;
+    const int h = blockIdx.x - bb * H;
+    const int i = threadIdx.x;
+    const int wi = i >> 5;
+    const int slot = p.slot_idx ? p.slot_idx[bb] : bb;
+    const int row0 = slot * p.rows_per_slot + h * HS;
+
+    if (i == 0) {
+        mbar_init(&bar, 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    if (i == 0) {
+        mbar_arrive_expect_tx(&bar, HS * HS * 2);
+        tma_load_2d(tile, &tm_state, 0, row0, &bar);
+    }
+    const int t0 = p.elapsed_t[bb];
+    const int c = h * HS + i;
+    const size_t idx = (size_t)bb * C + c;
+    {
+        const float kk_w = __half2float(p.k_k[c]), ka_w = __half2float(p.k_a[c]), rk_w = __half2float(p.r_k[c]);
+        pdl_wait();  // the state tile and the per-channel weights do not depend on the preceding kernels; r..g below do
+        FusedIn cur;
+        fused_load(cur, p, idx);
+        // ---- vector prep (rwkv7.py:632-637)
+        const float q = hr(cur.k * kk_w);
+        const float k2 = hr(cur.k * hr(1.0f + hr(hr(cur.a - 1.0f) * ka_w)));
+        const float v2 = p.v_first ? hr(cur.v + hr(hr(cur.vf - cur.v) * cur.vg)) : cur.v;
+        const float bonus_i = hr(hr(cur.r * k2) * rk_w);
+        const float s0 = warp_sum(q * q), s1 = warp_sum(bonus_i);
+        if ((i & 31) == 0) red[0][wi] = s0, red[1][wi] = s1;
+        __syncthreads();
+        const float nrm = hr(sqrtf(red[0][0] + red[0][1]));
+        const float kk = hr(q / nrm);
+        sv[0][i] = decay_dither(__float2half_rn(cur.w), t0);
+        sv[1][i] = __float2half_rn(k2);
+        sv[2][i] = __float2half_rn(-kk);
+        sv[3][i] = __float2half_rn(hr(kk * cur.a));
+        sv[4][i] = __float2half_rn(cur.r);
+        keep[0][i] = v2;
+        keep[1][i] = cur.g;
+        __syncthreads();
+    }
+    // ---- WKV-7 (identical to wkv7_seq_kernel)
+    mbar_wait(&bar, 0);
+    __half2 S[HS / 2];
+    {
+        const int4* rowp = reinterpret_cast<const int4*>(tile + i * 128);
+        const int sw = i & 7;
+#pragma unroll
+        for (int cc = 0; cc < 8; cc++) {
+            int4 qq = rowp[cc ^ sw];
+            S[4 * cc + 0] = *reinterpret_cast<__half2*>(&qq.x);
+            S[4 * cc + 1] = *reinterpret_cast<__half2*>(&qq.y);
+            S[4 * cc + 2] = *reinterpret_cast<__half2*>(&qq.z);
+            S[4 * cc + 3] = *reinterpret_cast<__half2*>(&qq.w);
+        }
+    }
+    const int4* wv = reinterpret_cast<const int4*>(sv[0]);
+    const int4* kv = reinterpret_cast<const int4*>(sv[1]);
+    const int4* av = reinterpret_cast<const int4*>(sv[2]);
+    const int4* bv = reinterpret_cast<const int4*>(sv[3]);
+    const int4* rv = reinterpret_cast<const int4*>(sv[4]);
+    __half2 acc = __floats2half2_rn(0.f, 0.f);
+#pragma unroll
+    for (int cc = 0; cc < 8; cc++) {
+        int4 qq = av[cc];
+        const __half2* pp = reinterpret_cast<const __half2*>(&qq);
+#pragma unroll
+        for (int u = 0; u < 4; u++) acc = __hfma2(pp[u], S[4 * cc + u], acc);
+    }
+    const __half2 sa2 = __half2half2(__hadd_rn(__low2half(acc), __high2half(acc)));
+    const __half2 vv2 = __half2half2(__float2half_rn(keep[0][i]));
+    acc = __floats2half2_rn(0.f, 0.f);
+    {
+        int4* rowp = reinterpret_cast<int4*>(tile + i * 128);
+        const int sw = i & 7;
+#pragma unroll
+        for (int cc = 0; cc < 8; cc++) {
+            int4 qw = wv[cc], qk = kv[cc], qb = bv[cc], qr = rv[cc];
+            const __half2* pw = reinterpret_cast<const __half2*>(&qw);
+            const __half2* pk = reinterpret_cast<const __half2*>(&qk);
+            const __half2* pb = reinterpret_cast<const __half2*>(&qb);
+            const __half2* pr = reinterpret_cast<const __half2*>(&qr);
+            int4 out;
+            __half2* po = reinterpret_cast<__half2*>(&out);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                __half2 s = S[4 * cc + u];
+                __half2 d = __hmul2_rn(pk[u], vv2);
+                d = __hfma2(s, pw[u], d);
+                d = __hfma2(sa2, pb[u], d);
+                s = __hadd2_rn(s, d);
+                po[u] = s;
+                acc = __hfma2(s, pr[u], acc);
+            }
+            rowp[cc ^ sw] = out;  // new state straight back into the swizzled tile
+        }
+    }
+    fence_proxy_async();
+    const float y = __half2float(__hadd_rn(__low2half(acc), __high2half(acc)));
+    // ---- GroupNorm over the head (eps 64e-5) + bonus + gate (rwkv7.py:647-649); the state write-back drains underneath
+    const float m0 = warp_sum(y), m1 = warp_sum(y * y);
+    if ((i & 31) == 0) red[2][wi] = m0, red[3][wi] = m1;
+    __syncthreads();
+    if (i == 0) {
+        tma_store_2d(&tm_state, 0, row0, tile);
+        tma_store_commit();
+    }
+    const float mean = (red[2][0] + red[2][1]) * (1.0f / 64.0f);
+    const float var = fmaxf((red[3][0] + red[3][1]) * (1.0f / 64.0f) - mean * mean, 0.0f);
+    const float rstd = 1.0f / sqrtf(var + 64e-5f);
+    const float gn = hr((y - mean) * rstd * __half2float(p.ln_w[c]) + __half2float(p.ln_b[c]));
+    const float bonus = hr(red[1][0] + red[1][1]);
+    const float o = hr(gn + hr(bonus * keep[0][i]));
+    p.out[idx] = __float2half_rn(hr(o * keep[1][i]));
+    if (i == 0) tma_store_wait_read<0>();  // the tile must stay valid until the bulk store has read it
+}
+
 }  // namespace
 
 int wkv7_make_state_tmap(CUtensorMap* tm, const void* state, int n_slots, int H, long state_slot_stride) {
@@ -351,6 +485,8 @@ int launch_wkv7_fused(const WkvFusedArgs& a, void* state, long state_slot_stride
     if (rc) return rc;
     WkvFusedArgs p = a;
     p.rows_per_slot = (int)(state_slot_stride / HS);
+    static const bool generic_only = getenv("B200_WKV_GENERIC") != nullptr;  // A/B switch
+    if (a.T == 1 && !generic_only) return launch_kernel(wkv7_fused_one_kernel, dim3(a.B * a.H), dim3(HS), 0, stream, pdl, 0, tm, p);
     return launch_kernel(wkv7_fused_kernel, dim3(a.B * a.H), dim3(HS), 0, stream, pdl, 0, tm, p);
 }
 
