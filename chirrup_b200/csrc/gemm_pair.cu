@@ -452,7 +452,8 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
     const int s = best_s;
     PairGroup grp;
     grp.n = n;
-    grp.n_stages = PAIR_MAX_STAGES;
+    static const int stages_env = getenv("B200_PAIR_STAGES") ? atoi(getenv("B200_PAIR_STAGES")) : PAIR_MAX_STAGES;
+    grp.n_stages = (s == 1 && stages_env >= 2 && stages_env <= PAIR_MAX_STAGES) ? stages_env : PAIR_MAX_STAGES;
     int end = 0;
     for (int i = 0; i < n; i++) {
         const int bn = best_bn[i];

@@ -27,6 +27,13 @@ DEVI H8 ld8(const __half* p) {
     for (int e = 0; e < 8; e++) o.f[e] = __half2float(h[e]);
     return o;
 }
+DEVI H8 cvt8(const int4& q) {
+    const __half* h = reinterpret_cast<const __half*>(&q);
+    H8 o;
+#pragma unroll
+    for (int e = 0; e < 8; e++) o.f[e] = __half2float(h[e]);
+    return o;
+}
 DEVI void st8(__half* p, const H8& v) {
     int4 q;
     __half* h = reinterpret_cast<__half*>(&q);
@@ -89,38 +96,90 @@ __global__ void embed_gather_kernel(int M, int C, const int* __restrict__ tokens
         *reinterpret_cast<int4*>(dst + c) = __ldg(reinterpret_cast<const int4*>(src + c));
 }
 
+// Sum of one float per thread over the block; every warp reduces the per-warp partials itself, so one barrier per call.
+// `part` must be a buffer (32 floats) not used by the previous block_sum1 call.
+DEVI float block_sum1(float v, float* part) {
+    v = warp_sum(v);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    if (lane == 0) part[warp] = v;
+    __syncthreads();
+    return warp_sum(lane < nw ? part[lane] : 0.f);
+}
+
+// LayerNorm (eps 1e-5, two-pass fp32 statistics as ATen) of one row held as 8 values per active thread, affine parameters
+// already in registers; result rounded to fp16.  Uses red[0..31] and red[32..63].
+DEVI H8 layer_norm8_pre(const H8& x, bool active, int C, const int4& wq, const int4& bq, float* red) {
+    float s = 0.f;
+    if (active) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) s += x.f[e];
+    }
+    const float mean = block_sum1(s, red) / (float)C;
+    float q = 0.f;
+    if (active) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            float d = x.f[e] - mean;
+            q += d * d;
+        }
+    }
+    const float var = block_sum1(q, red + 32) / (float)C;
+    const float rstd = 1.0f / sqrtf(var + 1e-5f);
+    const H8 ww = cvt8(wq), bb = cvt8(bq);
+    H8 o;
+#pragma unroll
+    for (int e = 0; e < 8; e++) o.f[e] = hr((x.f[e] - mean) * rstd * ww.f[e] + bb.f[e]);
+    return o;
+}
+
 // One CTA per (sequence b, token t) row.  cur = LN(x[b,t]); prev = t ? LN(x[b,t-1]) : shift_state[b];
 // out_n = cur + (prev - cur) * mix_n.  The t == 0 CTA also owns the shift state of its sequence: it reads the old value and
 // afterwards stores LN(x[b,T-1]) — no other CTA touches that row, so there is no ordering hazard for T > 1.
+// Everything that the preceding kernels of the step do not produce — LN affine, the lerp coefficients and the shift-state row
+// (last written by this same kernel one step earlier) — is fetched BEFORE griddepcontrol.wait, so under programmatic dependent
+// launch only the x row load and two one-barrier reductions remain on the critical path.
 template <int NMIX>
-__global__ void __launch_bounds__(1024) ln_shift_mix_kernel(int T, int C, const __half* __restrict__ x,
+__global__ void __launch_bounds__(512) ln_shift_mix_kernel(int T, int C, const __half* __restrict__ x,
                                                             const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
                                                             __half* __restrict__ shift, long shift_stride,
                                                             const int* __restrict__ slot_idx, MixPtrs<NMIX> mp) {
+    __shared__ float red[3 * 64];
     pdl_launch_dependents();
-    pdl_wait();
-    __shared__ float red[33];
     const int m = blockIdx.x;
     const int b = m / T, t = m - b * T;
     const int c0 = threadIdx.x * 8;
     const bool active = c0 < C;
     const __half* xrow = x + (size_t)m * C;
-    H8 xv;
-    if (active) xv = ld8(xrow + c0);
-    const H8 cur = layer_norm8(xv, active, C, ln_w, ln_b, c0, 1e-5f, red);
     __half* srow = shift + (size_t)(slot_idx ? slot_idx[b] : b) * shift_stride;
-    H8 prev;
+    // kept packed (8 fp16 per int4) until used: 9 x 4 registers instead of 9 x 8
+    const int4 z4 = make_int4(0, 0, 0, 0);
+    int4 ww = z4, bb = z4, mx[NMIX], prevq = z4;
+#pragma unroll
+    for (int n = 0; n < NMIX; n++) mx[n] = z4;
+    if (active) {
+        ww = *reinterpret_cast<const int4*>(ln_w + c0);
+        bb = *reinterpret_cast<const int4*>(ln_b + c0);
+#pragma unroll
+        for (int n = 0; n < NMIX; n++) mx[n] = *reinterpret_cast<const int4*>(mp.mix[n] + c0);
+        if (t == 0) prevq = *reinterpret_cast<const int4*>(srow + c0);
+    }
+    pdl_wait();
+    H8 prev = cvt8(prevq);
+    H8 xv;
+#pragma unroll
+    for (int e = 0; e < 8; e++) xv.f[e] = 0.f;
+    if (active) xv = ld8(xrow + c0);
+    const H8 cur = layer_norm8_pre(xv, active, C, ww, bb, red);
     if (t > 0) {
-        H8 pv;
+        H8 pv = xv;
         if (active) pv = ld8(xrow - C + c0);
-        prev = layer_norm8(pv, active, C, ln_w, ln_b, c0, 1e-5f, red);
+        prev = layer_norm8_pre(pv, active, C, ww, bb, red + 64);
     } else {
-        if (active) prev = ld8(srow + c0);
         H8 last = cur;
         if (T > 1) {
-            H8 lv;
+            H8 lv = xv;
             if (active) lv = ld8(xrow + (size_t)(T - 1) * C + c0);
-            last = layer_norm8(lv, active, C, ln_w, ln_b, c0, 1e-5f, red);
+            last = layer_norm8_pre(lv, active, C, ww, bb, red + 64);
         }
         if (active) st8(srow + c0, last);
     }
@@ -130,10 +189,10 @@ __global__ void __launch_bounds__(1024) ln_shift_mix_kernel(int T, int C, const 
     for (int e = 0; e < 8; e++) dx.f[e] = hr(prev.f[e] - cur.f[e]);
 #pragma unroll
     for (int n = 0; n < NMIX; n++) {
-        const H8 mx = ld8(mp.mix[n] + c0);
+        const H8 mv = cvt8(mx[n]);
         H8 o;
 #pragma unroll
-        for (int e = 0; e < 8; e++) o.f[e] = hr(cur.f[e] + hr(dx.f[e] * mx.f[e]));
+        for (int e = 0; e < 8; e++) o.f[e] = hr(cur.f[e] + hr(dx.f[e] * mv.f[e]));
         st8(mp.out[n] + (size_t)m * C + c0, o);
     }
 }
@@ -265,12 +324,14 @@ int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __ha
 int launch_ln_shift_mix6(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
                          long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl) {
     if (B * T <= 0) return 0;
+    if (C > 4096) return -4;  // B200_ERR_UNSUPPORTED: one thread per 8 channels, 512 threads (every RWKV-7 g1 size has C <= 4096)
     return launch_kernel(ln_shift_mix_kernel<6>, dim3(B * T), dim3(ln_threads(C)), 0, s, pdl, 0, T, C, x, ln_w, ln_b, shift,
                          shift_stride, slot_idx, mp);
 }
 int launch_ln_shift_mix1(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
                          long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s, bool pdl) {
     if (B * T <= 0) return 0;
+    if (C > 4096) return -4;
     return launch_kernel(ln_shift_mix_kernel<1>, dim3(B * T), dim3(ln_threads(C)), 0, s, pdl, 0, T, C, x, ln_w, ln_b, shift,
                          shift_stride, slot_idx, mp);
 }

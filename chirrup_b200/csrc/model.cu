@@ -64,6 +64,7 @@ extern "C" int b200_model_create(int n_layer, int n_embd, int vocab_size, int d_
                                  const void* const* global_w, const void* const* layer_w, b200_model** out) {
     if (!out || !global_w || !layer_w || n_layer <= 0 || n_embd <= 0 || (n_embd % 64) || vocab_size <= 0 || (vocab_size & 7))
         return B200_ERR_BAD_ARG;
+    if (n_embd > 4096) return B200_ERR_UNSUPPORTED;  // ln_shift_mix: one thread per 8 channels, 512 threads (RWKV-7 g1: C <= 4096)
     if (d_w <= 0 || d_a <= 0 || d_v <= 0 || d_g <= 0 || (d_w & 7) || (d_a & 7) || (d_v & 7) || (d_g & 7)) return B200_ERR_BAD_ARG;
     b200_model* m = new (std::nothrow) b200_model();
     if (!m) return B200_ERR_BAD_ARG;
