@@ -361,7 +361,7 @@ def main():
             "e2e": {"value": e2e, "unit": "tok/s", "h2d_bytes_per_step": a.bsz * 4, "d2h_bytes_per_step": a.bsz * 4,
                     "api": "RWKV_x070.forward_seq_batch_seperate(host token ids) + greedy sample + D2H of the ids"},
             "gpu_launches": r["launches"], "cuda_graph": r["graph"], "clocks": r["clocks"],
-            "roofline": {"bound": "hbm", "kernel": "wkv7_fused_kernel (T=1): kk-normalise + k,v mix + WKV-7 state update + GroupNorm + bonus + gate",
+            "roofline": {"bound": "hbm", "kernel": "wkv7_fused_one_kernel (T=1): kk-normalise + k,v mix + WKV-7 state update + GroupNorm + bonus + gate",
                          "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "frac_of_8TBps_nominal": achieved / 8000.0, "traffic": traffic, "peak_source": which,
                          "algorithmic_bytes_per_launch": fused_bytes, "us_per_launch": r["wkv_s"]["fused"] * 1e6,
