@@ -37,6 +37,7 @@ SIGNATURES: Dict[str, tuple] = {
     "b200_model_forward": (_I, [_P, _I, _I, _P, _P, _L, _L, _P, _L, _I, _P, _P, _P, _I, _P, _L, _P]),
     "b200_model_last_launch_count": (_I, [_P]),
     "b200_argmax_f16": (_I, [_I, _I, _P, _L, _P, _P]),
+    "b200_sample_f16": (_I, [_I, _I, _P, _L, _P, _P, _P]),
 }
 
 
@@ -44,6 +45,14 @@ class LinearDesc(ctypes.Structure):
     """``b200_linear_desc`` of include/chirrup_b200.h."""
     _fields_ = [("N", _I), ("K", _I), ("A", _P), ("lda", _L), ("W", _P), ("ldw", _L), ("out", _P), ("ldo", _L),
                 ("bias", _P), ("residual", _P), ("epilogue", _I)]
+
+
+class SampleParams(ctypes.Structure):
+    """``b200_sample_params`` of include/chirrup_b200.h."""
+    _fields_ = [("slot", _P), ("occurrence", _P), ("presence", _P), ("penalty_decay", _P), ("frequency_penalty", _P),
+                ("presence_penalty", _P), ("temperature", _P), ("top_p", _P), ("top_k", _P), ("forbidden", _P),
+                ("max_forbidden", _I), ("no_penalty", _P), ("n_no_penalty", _I), ("seed", _c.c_ulonglong),
+                ("step", _c.c_ulonglong), ("kept", _P)]
 
 
 def header_symbols() -> List[str]:

@@ -179,3 +179,55 @@ def linear_group(xs, Ws, biases=None, epilogues=None, residuals=None, outs=None)
     rc = _lib.lib().b200_linear_group_f16(n, ctypes.cast(descs, ctypes.c_void_p), M, ws.data_ptr(), ws.numel(), _stream(xs[0]))
     _lib.check(rc, "b200_linear_group_f16")
     return res
+
+
+def sample(logits: torch.Tensor, temperature: Optional[torch.Tensor] = None, top_p: Optional[torch.Tensor] = None,
+           top_k: Optional[torch.Tensor] = None, *, slot: Optional[torch.Tensor] = None,
+           occurrence: Optional[torch.Tensor] = None, presence: Optional[torch.Tensor] = None,
+           penalty_decay: Optional[torch.Tensor] = None, frequency_penalty: Optional[torch.Tensor] = None,
+           presence_penalty: Optional[torch.Tensor] = None, forbidden: Optional[torch.Tensor] = None,
+           no_penalty: Optional[torch.Tensor] = None, seed: int = 0, step: int = 0, return_kept: bool = False):
+    """One decode sampling step (``b200_sample_f16``): the worker's penalty block (``chirrup/worker.py:713-740``), its sampler
+    (``chirrup/utils/samplers.py:98-168``) and the penalty update of the drawn token (``worker.py:527-547``) in one kernel.
+    ``logits`` fp16 (rows, V) is penalised IN PLACE; per-slot parameter tensors are 1-D (n_slots) — fp32, ``top_k`` int32 —
+    indexed by ``slot`` (int32 (rows), default: row index); ``occurrence`` / ``presence`` fp32 (n_slots, V) are updated in place;
+    ``forbidden`` int32 (rows, F) padded with -1.  Returns int32 (rows) token ids (and the kept-set sizes if asked)."""
+    _req(logits, "logits")
+    if logits.dim() != 2 or logits.stride(1) != 1:
+        raise ValueError("logits must be (rows, V) with unit inner stride")
+    rows, V = logits.shape
+    dev = logits.device
+    P = _lib.SampleParams()
+
+    def ptr(t, name, dtype, numel=None):
+        if t is None:
+            return None
+        _req(t, name, dtype)
+        if not t.is_contiguous():
+            raise ValueError(f"{name} must be contiguous")
+        if numel is not None and t.numel() < numel:
+            raise ValueError(f"{name} too small")
+        return t.data_ptr()
+
+    P.slot = ptr(slot, "slot", torch.int32, rows)
+    P.occurrence = ptr(occurrence, "occurrence", torch.float32)
+    P.presence = ptr(presence, "presence", torch.float32)
+    if occurrence is not None and (occurrence.dim() != 2 or occurrence.shape[1] != V or presence is None or presence.shape != occurrence.shape):
+        raise ValueError("occurrence / presence must both be (n_slots, V)")
+    P.penalty_decay = ptr(penalty_decay, "penalty_decay", torch.float32)
+    P.frequency_penalty = ptr(frequency_penalty, "frequency_penalty", torch.float32)
+    P.presence_penalty = ptr(presence_penalty, "presence_penalty", torch.float32)
+    P.temperature = ptr(temperature, "temperature", torch.float32)
+    P.top_p = ptr(top_p, "top_p", torch.float32)
+    P.top_k = ptr(top_k, "top_k", torch.int32)
+    P.forbidden = ptr(forbidden, "forbidden", torch.int32)
+    P.max_forbidden = 0 if forbidden is None else (forbidden.shape[1] if forbidden.dim() == 2 and forbidden.shape[0] == rows else -1)
+    P.no_penalty = ptr(no_penalty, "no_penalty", torch.int32)
+    P.n_no_penalty = 0 if no_penalty is None else no_penalty.numel()
+    P.seed, P.step = seed & (2 ** 64 - 1), step & (2 ** 64 - 1)
+    kept = torch.empty((rows,), dtype=torch.int32, device=dev) if return_kept else None
+    P.kept = kept.data_ptr() if kept is not None else None
+    out = torch.empty((rows,), dtype=torch.int32, device=dev)
+    rc = _lib.lib().b200_sample_f16(rows, V, logits.data_ptr(), logits.stride(0), ctypes.byref(P), out.data_ptr(), _stream(logits))
+    _lib.check(rc, "b200_sample_f16")
+    return (out, kept) if return_kept else out

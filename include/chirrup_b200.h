@@ -171,6 +171,36 @@ int b200_model_forward(b200_model* m, int B, int T, const int* tokens, void* sta
  * The top_k == 1 case of the worker's sampler (chirrup/worker.py:733-740, chirrup/utils/samplers.py:171-255). */
 int b200_argmax_f16(int rows, int V, const void* logits, long ld, int* out, void* stream);
 
+/*
+ * One decode SAMPLING step for `rows` logit rows in one kernel (one CTA per row, no sort): what chirrup/worker.py:713-740 does
+ * to the decode logits (forbidden tokens -= 1e10; occurrence *= penalty_decay; logits -= alpha_presence + occurrence *
+ * frequency_penalty — in place, fp32 math, one fp16 rounding per op), then chirrup/utils/samplers.py:98-168
+ * (sample_logits_real_batch: softmax(logits / temperature), keep sorted rank < top_k (top_k <= 0: no limit) and cumulative
+ * probability <= top_p (top_p >= 1: no limit), always at least one token, draw proportionally), then
+ * chirrup/worker.py:527-547 for the drawn token (occurrence += 1 unless the token is in no_penalty; alpha_presence =
+ * presence_penalty).  Rows with top_k == 1, top_p <= 0 or temperature <= 0 take the arg-max (lowest index).
+ * All pointers are device pointers; the struct itself is read on the host.  Per-slot arrays are indexed by slot[i] (NULL: i).
+ * The draw is a pure function of (seed, step, row index): Philox4x32-10.  V <= 65536, V % 8 == 0.
+ */
+typedef struct b200_sample_params {
+    const int* slot;                 /* int32 (rows) or NULL */
+    float* occurrence;               /* fp32 (n_slots, V) or NULL: no penalties */
+    float* presence;                 /* fp32 (n_slots, V) alpha_presence_vector; NULL iff occurrence is NULL */
+    const float* penalty_decay;      /* fp32 (n_slots) */
+    const float* frequency_penalty;  /* fp32 (n_slots) */
+    const float* presence_penalty;   /* fp32 (n_slots) */
+    const float* temperature;        /* fp32 (n_slots) or NULL (1.0) */
+    const float* top_p;              /* fp32 (n_slots) or NULL (1.0) */
+    const int* top_k;                /* int32 (n_slots) or NULL (0) */
+    const int* forbidden;            /* int32 (rows, max_forbidden), padded with -1, or NULL */
+    int max_forbidden;               /* <= 512 */
+    const int* no_penalty;           /* int32 (n_no_penalty) token ids whose occurrence is not incremented, or NULL */
+    int n_no_penalty;
+    unsigned long long seed, step;
+    int* kept;                       /* optional int32 (rows): size of the kept set (tests / debugging) */
+} b200_sample_params;
+int b200_sample_f16(int rows, int V, void* logits, long ld, const b200_sample_params* params, int* out, void* stream);
+
 /* Number of kernels the last b200_model_forward on this model launched (bench.py reports it as gpu_launches). */
 int b200_model_last_launch_count(const b200_model* m);
 
