@@ -9,9 +9,10 @@
 * decode step = ``forward`` over the DECODE + ONE_PREFILL slots with T = 1 (worker.py:671-742); prefill = up to
   ``max_forward_seq_len_per_forward`` = 100 tokens of every SEQ slot, every ``decode_prefill_ratio`` = 5 decode steps
   (worker.py:173-179, :744-776, :854-856); admission of at most ``max_prefill_count`` new tasks per loop (worker.py:143, :570-669);
-* greedy requests (top_k == 1 or temperature == 0 or top_p == 0) are sampled by the C-ABI argmax kernel with ONE batched D2H
-  per step instead of one ``.item()`` per slot (worker.py:738-740); other requests use a torch nucleus sampler after the
-  reference's penalty formula (worker.py:527-547, :719-728) — sampling is downstream of the hot path.
+* sampling is ONE kernel and ONE batched D2H per step instead of a full sort, two (B,V) fp32 temporaries and one ``.item()`` per
+  slot (worker.py:713-740): the arg-max kernel when every row is greedy without penalties, else the fused sampling kernel
+  ``b200_sample_f16`` (forbidden mask, decay + presence / frequency penalties, temperature, top-k, top-p, draw, penalty update;
+  samplers.py:98-168, worker.py:527-547) over device-resident per-slot parameters and penalty rows.
 
 One worker per GPU, all pulling from one task queue (engine_core.py:71, :135-153): request-level data parallelism, no collective.
 """
@@ -164,7 +165,10 @@ class Worker:
         self.model = model
         self.slots: List[_Slot] = [_Slot() for _ in range(batch_size)]
         self.steps = {"decode": 0, "prefill": 0, "decode_tokens": 0, "prefill_tokens": 0}
-        self._occurrence = None
+        self._occurrence = None                               # device penalty state, allocated with the first non-plain request
+        self._occ_host = None
+        self._par_dirty = False
+        self.sample_seed = 0x5EED0000 + sum(map(ord, str(worker_id)))
         self._stop = False
 
     # ------------------------------------------------------------------ init
@@ -221,8 +225,9 @@ class Worker:
                 state_move.clear_slot(self.batch_state, pos)                     # generate_zero_state(1), worker.py:586-589
             else:
                 state_move.inject_slot(self.batch_state, pos, task.state)        # task.state[i].cuda(), worker.py:591-597
-            if self._occurrence is not None:
-                self._occurrence[pos].zero_()
+            self._set_slot_params(pos, task)
+            if self._occ_host is not None:
+                self._occ_host[pos].zero_()
             toks = list(task.prefill_tokens) or [0]
             slot.task, slot.pending = task, toks
             task.request_status = RequestStatus.RUNNING
@@ -256,34 +261,95 @@ class Worker:
         self.steps["prefill_tokens"] += T * len(seq)
         return T * len(seq)
 
+    # ------------------------------------------------------------------ sampling
+    def _sampling_state(self, V: int) -> None:
+        """Penalty state and per-slot sampler parameters on the device (worker.py:262-300: occurrence, alpha_presence_vector,
+        temperature / top_p / top_k / penalty tensors, one row per slot) plus pinned host mirrors of the parameters."""
+        if self._occurrence is not None:
+            return
+        dev, n = self.device, self.batch_size
+        self._occurrence = torch.zeros((n, V), dtype=torch.float32, device=dev)
+        self._presence = torch.zeros((n, V), dtype=torch.float32, device=dev)
+        self._par_host = torch.zeros((6, n), dtype=torch.float32).pin_memory()   # temperature, top_p, decay, freq, presence, top_k
+        self._par_dev = torch.zeros((6, n), dtype=torch.float32, device=dev)
+        self._topk_dev = torch.zeros((n,), dtype=torch.int32, device=dev)
+        self._par_dirty = True
+        for pos, sl in enumerate(self.slots):
+            if sl.task is not None:
+                self._set_slot_params(pos, sl.task)
+
+    def _set_slot_params(self, pos: int, t: Task) -> None:
+        """Per-slot sampler parameters of a newly admitted task (worker.py:599-640) and a clean penalty row."""
+        if self._occurrence is None:
+            return
+        greedy = t.is_greedy()
+        h = self._par_host
+        h[0, pos] = 1.0 if greedy else t.temperature
+        h[1, pos] = 1.0 if greedy else t.top_p
+        h[2, pos], h[3, pos], h[4, pos] = t.penalty_decay, t.frequency_penalty, t.presence_penalty
+        h[5, pos] = 1.0 if greedy else float(max(t.top_k, 0))
+        self._occurrence[pos].zero_()
+        self._presence[pos].zero_()
+        self._par_dirty = True
+
     def _sample(self, rows: List[int], logits: torch.Tensor) -> List[int]:
-        """Next token for each row of `logits` (row i belongs to slot rows[i]).  Greedy rows: the C-ABI argmax kernel and ONE
-        batched D2H.  Others: forbidden-token mask + presence/frequency penalties with decay (worker.py:527-547, :719-728),
-        temperature, nucleus top-p / top-k, multinomial — in torch, outside the hot path."""
+        """Next token for each row of `logits` (row i belongs to slot rows[i]).  On the GPU one C-ABI call and ONE batched D2H per
+        step: the arg-max kernel when every row is greedy with zero penalties, else the fused sampling kernel
+        (``b200_sample_f16``: forbidden mask + decay / presence / frequency penalties on every decode row, temperature, top-k,
+        top-p, draw, penalty update — worker.py:713-740, samplers.py:98-168, worker.py:527-547)."""
         from . import ops
 
         n = len(rows)
-        if logits.is_cuda:
+        tasks = [self.slots[p].task for p in rows]
+        if not logits.is_cuda:                                                   # CPU test double of the model: host logic only
+            return self._sample_host(rows, logits)
+        plain = all(t is None or (t.is_greedy() and t.presence_penalty == 0 and t.frequency_penalty == 0
+                                  and not t.forbidden_tokens) for t in tasks)
+        if plain:
             ids = ops.argmax(logits)
-            self._out_host[:n].copy_(ids, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-            out = self._out_host[:n].tolist()
-        else:                                                                    # CPU test double of the model
-            out = logits.float().argmax(-1).tolist()
+        else:
+            V = logits.shape[1]
+            self._sampling_state(V)
+            if self._par_dirty:
+                self._par_dev.copy_(self._par_host, non_blocking=True)
+                self._topk_dev.copy_(self._par_dev[5].to(torch.int32))
+                self._par_dirty = False
+            slot = torch.tensor(rows, dtype=torch.int32, device=self.device)
+            forb = None
+            nf = max((len(t.forbidden_tokens) for t in tasks if t is not None), default=0)
+            if nf:
+                fh = torch.full((n, nf), -1, dtype=torch.int32)
+                for i, t in enumerate(tasks):
+                    if t is not None and t.forbidden_tokens:
+                        fh[i, :len(t.forbidden_tokens)] = torch.tensor(t.forbidden_tokens, dtype=torch.int32)
+                forb = fh.to(self.device)
+            if not logits.is_contiguous():
+                logits = logits.contiguous()
+            pd = self._par_dev
+            ids = ops.sample(logits, pd[0], pd[1], self._topk_dev, slot=slot, occurrence=self._occurrence, presence=self._presence,
+                             penalty_decay=pd[2], frequency_penalty=pd[3], presence_penalty=pd[4], forbidden=forb,
+                             seed=self.sample_seed, step=self.steps["decode"])
+        self._out_host[:n].copy_(ids, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self._out_host[:n].tolist()
+
+    def _sample_host(self, rows: List[int], logits: torch.Tensor) -> List[int]:
+        """torch restatement of the same step for the CPU test double (never runs on the product path)."""
+        out = logits.float().argmax(-1).tolist()
         for i, p in enumerate(rows):
             t = self.slots[p].task
             if t is None or t.is_greedy():
                 continue
-            if self._occurrence is None:
-                self._occurrence = torch.zeros((self.batch_size, logits.shape[1]), dtype=torch.float32, device=logits.device)
-            occ = self._occurrence[p]
+            if self._occ_host is None:
+                self._occ_host = torch.zeros((self.batch_size, logits.shape[1]), dtype=torch.float32)
+            occ = self._occ_host[p]
             lg = logits[i].float()
             if t.forbidden_tokens:
-                lg[torch.tensor(t.forbidden_tokens, device=lg.device)] -= 1e10
+                lg[torch.tensor(t.forbidden_tokens)] -= 1e10
             lg = lg - t.presence_penalty * (occ > 0).float() - t.frequency_penalty * occ
             probs = torch.softmax(lg / max(t.temperature, 1e-6), dim=-1)
             sp, si = torch.sort(probs, descending=True)
-            keep = (torch.cumsum(sp, 0) - sp) < t.top_p
+            keep = torch.cumsum(sp, 0) <= t.top_p
             if t.top_k > 0:
                 keep[t.top_k:] = False
             keep[0] = True

@@ -52,7 +52,8 @@ def test_worker_continuous_batching_matches_isolated_greedy():
 
     sinks = [Sink() for _ in prompts]
     for p, s in zip(prompts, sinks):
-        w.task_queue.put(Task(prefill_tokens=p, output_queue=s, top_k=1, max_tokens=12, stop_tokens=[]))
+        w.task_queue.put(Task(prefill_tokens=p, output_queue=s, top_k=1, max_tokens=12, stop_tokens=[], presence_penalty=0.0,
+                              frequency_penalty=0.0))
     for _ in range(2000):
         w.step()
         if not w.busy() and w.task_queue.empty():
@@ -73,7 +74,8 @@ def test_async_engine_core_end_to_end():
     async def main():
         eng = AsyncEngineCore()
         await eng.init(worker_num=1, model_config=ModelLoadConfig(state_dict=raw, vocab_size=geom.vocab_size), batch_size=8)
-        comps = [eng.completion(prefill_tokens=[5 + i, 9, 11], top_k=1, max_tokens=6, stop_tokens=[]) for i in range(12)]
+        comps = [eng.completion(prefill_tokens=[5 + i, 9, 11], top_k=1, max_tokens=6, stop_tokens=[], presence_penalty=0.0,
+                                frequency_penalty=0.0) for i in range(12)]
         outs = await asyncio.gather(*[c.get_full_completion() for c in comps])
         eng.shutdown()
         return outs, [c.finish_reason for c in comps], eng.workers[0].model
@@ -145,3 +147,83 @@ def test_reference_op_names_run_on_our_kernels():
     out = torch.zeros(256, dtype=torch.float16, device="cuda")
     torch.ops.rwkv7_state_fwd_fp16.spmv_forward(512, 256, vec, mat, out)
     assert torch.equal(out, ops.spmv_forward(vec, mat))
+
+
+def _run_worker(m, tasks, batch_size=4):
+    from chirrup_b200.engine import ModelLoadConfig, Worker
+
+    class Sink:
+        def __init__(self):
+            self.items = []
+
+        def put_nowait(self, x):
+            self.items.append(x)
+
+    w = Worker("w0", [0], ModelLoadConfig(), queue.Queue(), batch_size=batch_size, model=m)
+    w._init_worker()
+    sinks = [Sink() for _ in tasks]
+    for t, s in zip(tasks, sinks):
+        t.output_queue = s
+        w.task_queue.put(t)
+    for _ in range(4000):
+        w.step()
+        if not w.busy() and w.task_queue.empty():
+            break
+    assert not w.busy()
+    return [[e[1] for e in s.items if e[0] == "token"] for s in sinks], w
+
+
+def test_worker_penalised_greedy_matches_reference_penalty_formula():
+    """top_k = 1 requests WITH presence / frequency penalties, decay and forbidden tokens through the fused sampling kernel
+    (device-resident per-slot penalty rows, slot indirection) against a per-request loop over the same model with the oracle's
+    restatement of the reference's penalty block (worker.py:719-728) and update (worker.py:527-547): token-identical."""
+    from chirrup_b200.engine import Task
+    from oracle import sampler_oracle as SO
+
+    geom, m = _model("small", seed=3)
+    V = geom.vocab_size
+    g = torch.Generator().manual_seed(1)
+    specs = [(5, 0.5, 0.5, 0.996, []), (17, 2.0, 0.3, 0.9, [3, 9]), (2, 0.0, 1.5, 1.0, []), (130, 0.7, 0.0, 0.5, [11]),
+             (40, 0.4, 0.6, 0.996, []), (9, 1.0, 1.0, 0.95, [])]
+    prompts = [torch.randint(1, V, (n,), generator=g).tolist() for n, *_ in specs]
+    n_new = 24
+    tasks = [Task(prefill_tokens=p, top_k=1, max_tokens=n_new, stop_tokens=[], presence_penalty=pp, frequency_penalty=fp,
+                  penalty_decay=dc, forbidden_tokens=fb) for p, (_, pp, fp, dc, fb) in zip(prompts, specs)]
+    got, w = _run_worker(m, tasks, batch_size=4)
+    for p, (_, pp, fp, dc, fb), toks in zip(prompts, specs, got):
+        st = m.generate_zero_state(1)
+        lg = m.forward_seq_batch([p], st)
+        occ, alpha = torch.zeros(1, V), torch.zeros(1, V)
+        want = []
+        for _ in range(n_new):
+            row = lg.cpu().clone()
+            SO.penalise(row, occ, alpha, torch.tensor([[dc]]), torch.tensor([[fp]]), [fb])
+            t = int(row.float().argmax(-1)[0])
+            want.append(t)
+            SO.update_penalty(occ, alpha, torch.tensor([[pp]]), [0], [t])
+            lg = m.forward_seq_batch([[t]], st)
+        assert toks == want, (len(p), toks[:8], want[:8])
+        assert not set(fb) & set(toks)
+
+
+def test_worker_sampled_requests_are_reproducible_and_respect_top_k():
+    """Non-greedy requests: same worker seed -> same tokens (the draw is a pure function of seed, step and row); with top_k = 3
+    and no penalties every drawn token is one of the three most likely ones of a replay of the same sequence."""
+    from chirrup_b200.engine import Task
+
+    geom, m = _model("small", seed=4)
+    V = geom.vocab_size
+    g = torch.Generator().manual_seed(2)
+    prompts = [torch.randint(1, V, (n,), generator=g).tolist() for n in (4, 21, 7)]
+    mk = lambda: [Task(prefill_tokens=p, temperature=1.3, top_p=0.95, top_k=3, max_tokens=16, stop_tokens=[], presence_penalty=0.0,
+                       frequency_penalty=0.0) for p in prompts]
+    a, _ = _run_worker(m, mk())
+    b, _ = _run_worker(m, mk())
+    assert a == b
+    for p, toks in zip(prompts, a):
+        st = m.generate_zero_state(1)
+        lg = m.forward_seq_batch([p], st)
+        for t in toks:
+            assert t in torch.topk(lg.float()[0], 3).indices.tolist()
+            lg = m.forward_seq_batch([[t]], st)
+    assert len({tuple(x) for x in a}) > 1
