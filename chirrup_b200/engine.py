@@ -168,6 +168,9 @@ class Worker:
         self._occurrence = None                               # device penalty state, allocated with the first non-plain request
         self._occ_host = None
         self._par_dirty = False
+        self._inflight: Optional[Dict[str, Any]] = None       # decode step launched, host side not yet done
+        self._rows_cache = None
+        self.pipeline = True
         self.sample_seed = 0x5EED0000 + sum(map(ord, str(worker_id)))
         self._stop = False
 
@@ -186,7 +189,7 @@ class Worker:
                 args = make_args(self.model_config.model_path, self.model_config.vocab_size, self.model_config.head_size)
                 self.model = RWKV_x070(args, state_dict=self.model_config.state_dict, device=self.device)
         self.batch_state = self.model.generate_zero_state(self.batch_size)      # worker.py:260
-        self._out_host = torch.empty((self.batch_size,), dtype=torch.int32)
+        self._out_host = torch.empty((2, self.batch_size), dtype=torch.int32)    # double-buffered: one per step in flight
         if self.device.type == "cuda":
             self._out_host = self._out_host.pin_memory()
         if self.master_event_queue is not None:
@@ -292,9 +295,10 @@ class Worker:
         self._presence[pos].zero_()
         self._par_dirty = True
 
-    def _sample(self, rows: List[int], logits: torch.Tensor) -> List[int]:
-        """Next token for each row of `logits` (row i belongs to slot rows[i]).  On the GPU one C-ABI call and ONE batched D2H per
-        step: the arg-max kernel when every row is greedy with zero penalties, else the fused sampling kernel
+    def _sample_launch(self, rows: List[int], logits: torch.Tensor) -> torch.Tensor:
+        """Next token for each row of `logits` (row i belongs to slot rows[i]) as an int32 tensor on the model's device, without
+        any host synchronisation.  On the GPU one C-ABI call per step: the arg-max kernel when every row is greedy with zero
+        penalties, else the fused sampling kernel
         (``b200_sample_f16``: forbidden mask + decay / presence / frequency penalties on every decode row, temperature, top-k,
         top-p, draw, penalty update — worker.py:713-740, samplers.py:98-168, worker.py:527-547)."""
         from . import ops
@@ -302,7 +306,7 @@ class Worker:
         n = len(rows)
         tasks = [self.slots[p].task for p in rows]
         if not logits.is_cuda:                                                   # CPU test double of the model: host logic only
-            return self._sample_host(rows, logits)
+            return torch.tensor(self._sample_host(rows, logits), dtype=torch.int32)
         plain = all(t is None or (t.is_greedy() and t.presence_penalty == 0 and t.frequency_penalty == 0
                                   and not t.forbidden_tokens) for t in tasks)
         if plain:
@@ -329,9 +333,7 @@ class Worker:
             ids = ops.sample(logits, pd[0], pd[1], self._topk_dev, slot=slot, occurrence=self._occurrence, presence=self._presence,
                              penalty_decay=pd[2], frequency_penalty=pd[3], presence_penalty=pd[4], forbidden=forb,
                              seed=self.sample_seed, step=self.steps["decode"])
-        self._out_host[:n].copy_(ids, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return self._out_host[:n].tolist()
+        return ids
 
     def _sample_host(self, rows: List[int], logits: torch.Tensor) -> List[int]:
         """torch restatement of the same step for the CPU test double (never runs on the product path)."""
@@ -370,40 +372,127 @@ class Worker:
             t.output_queue.put_nowait(("finish", reason, t))
         self.slots[pos] = _Slot()                                                # -> EMPTY
 
+    def _launch_decode(self, rows: List[int], feed: Optional[torch.Tensor]) -> Dict[str, Any]:
+        """Enqueue one T = 1 step over `rows` (worker.py:671-742): forward, sampling and the D2H of the drawn ids into a pinned
+        buffer — NO host synchronisation.  `feed` = the previous step's device-resident ids when they are exactly the input
+        tokens of this step (every row decoding, same rows), else None: tokens come from the host-side slot table."""
+        n = len(rows)
+        if feed is None:
+            toks = []
+            for p in rows:
+                s = self.slots[p]
+                toks.append([s.pending.pop(0) if s.pending else s.next_token])
+            tok_dev = self.model._tokens(toks)
+        else:
+            ids_prev, pos_in_prev = feed
+            if ids_prev.numel() == n and len(pos_in_prev) == n and all(pos_in_prev.get(p) == i for i, p in enumerate(rows)):
+                tok_dev = ids_prev                                              # same rows, all decoding: no host data at all
+            else:                                                               # rows left / joined: gather on the device
+                src, host = [], []
+                for p in rows:
+                    s = self.slots[p]
+                    if s.pending:
+                        host.append(s.pending.pop(0))
+                        src.append(-1)
+                    else:
+                        host.append(0)
+                        src.append(pos_in_prev[p])
+                both = torch.tensor([src, host], dtype=torch.int32).to(self.device, non_blocking=True)
+                tok_dev = torch.where(both[0] >= 0, ids_prev[both[0].clamp(min=0).long()], both[1]).contiguous()
+        if self._rows_cache is None or self._rows_cache[0] != rows:
+            self._rows_cache = (list(rows), torch.tensor(rows, dtype=torch.int32, device=self.device))
+        idx = self._rows_cache[1]
+        st, el = self._state_for(idx)
+        logits = self.model._step(tok_dev, n, 1, st, False, slot_idx=idx)
+        self.batch_state[2][idx.long()] = el
+        sample_rows = [i for i, p in enumerate(rows) if not self.slots[p].pending]    # prompt fully consumed: logits count
+        rec: Dict[str, Any] = {"rows": list(rows), "tasks": [self.slots[p].task for p in rows], "sample_rows": sample_rows,
+                               "ids": None, "host": None, "event": None, "logits": None}
+        if sample_rows:
+            sel = logits if len(sample_rows) == n else logits[torch.tensor(sample_rows, device=logits.device)]
+            if any(self.slots[rows[i]].task.return_logits for i in sample_rows):
+                rec["logits"] = sel.detach().clone()                                 # before the in-place penalties
+            ids = self._sample_launch([rows[i] for i in sample_rows], sel)
+            rec["ids"] = ids
+            if ids.is_cuda:
+                buf = self._out_host[self.steps["decode"] & 1]
+                buf[:len(sample_rows)].copy_(ids, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                rec["host"], rec["event"] = buf, ev
+            else:
+                rec["host"] = ids
+        self.steps["decode"] += 1
+        return rec
+
+    def _finish_decode(self, rec: Dict[str, Any]) -> int:
+        """Host side of a launched step: wait for ITS ids only, deliver tokens, stop / length checks (worker.py:478-510, :738-742).
+        Rows whose slot no longer holds the task the step was launched for (finished or aborted meanwhile) are dropped."""
+        rows, sample_rows = rec["rows"], rec["sample_rows"]
+        if not sample_rows:
+            return 0
+        if rec["event"] is not None:
+            rec["event"].synchronize()
+        new = rec["host"][:len(sample_rows)].tolist()
+        delivered = 0
+        for j, (i, tok) in enumerate(zip(sample_rows, new)):
+            p = rows[i]
+            s = self.slots[p]
+            t = s.task
+            if t is None or t is not rec["tasks"][i]:
+                continue
+            s.next_token = tok
+            s.category = StateCategory.FORWARD_ONE_DECODE
+            t.generated_tokens.append(tok)
+            delivered += 1
+            if t.output_queue is not None:
+                t.output_queue.put_nowait(("token", tok, self.tokenizer.decode([tok]),
+                                           rec["logits"][j] if (t.return_logits and rec["logits"] is not None) else None))
+            if tok in t.stop_tokens:
+                self._finish(p, RequestStatus.FINISHED_STOPPED)
+            elif t.max_tokens is not None and len(t.generated_tokens) >= t.max_tokens:
+                self._finish(p, RequestStatus.FINISHED_LENGTH_CAPPED)
+        self.steps["decode_tokens"] += delivered
+        return delivered
+
     def _run_forward_one(self) -> int:
-        """One T = 1 step over the DECODE and ONE_PREFILL groups (worker.py:671-742)."""
+        """One T = 1 step over the DECODE and ONE_PREFILL groups (worker.py:671-742), software-pipelined one step deep: when the
+        step in flight covers exactly the rows that decode next, the NEXT step is enqueued first — its input tokens are the
+        in-flight step's ids, still on the device — and only then is the in-flight step's host work done, under the GPU time
+        of the next one.  A request that finishes is noticed one step late; the extra token computed for it is dropped."""
         groups, _ = group_slots(self.categories())
         dec, pre = groups[StateCategory.FORWARD_ONE_DECODE], groups[StateCategory.FORWARD_ONE_PREFILL]
         rows = dec + pre                                                         # decode rows first, like the reference's layout
+        prev, self._inflight = self._inflight, None
+        if prev is not None and self.pipeline and prev["ids"] is not None:
+            prow, ptask = prev["rows"], prev["tasks"]
+            pos_in_prev = {}                                                     # slot -> position of its id in the in-flight step
+            for j, i in enumerate(prev["sample_rows"]):
+                p = prow[i]
+                if self.slots[p].task is ptask[i] and not self.slots[p].pending:
+                    pos_in_prev[p] = j
+
+            def capped(p):                                                       # the in-flight token is this request's last one
+                t = self.slots[p].task
+                return p in pos_in_prev and t.max_tokens is not None and len(t.generated_tokens) + 1 >= t.max_tokens
+
+            nxt = [p for p in rows if not capped(p)]
+            # every row's input token must be known without waiting: on the device (in-flight id) or in its prompt
+            if nxt and all(p in pos_in_prev or self.slots[p].pending for p in nxt):
+                self._inflight = self._launch_decode(nxt, (prev["ids"], {p: pos_in_prev[p] for p in nxt if p in pos_in_prev}))
+                self._finish_decode(prev)
+                return len(nxt)
+        if prev is not None:
+            self._finish_decode(prev)
+            groups, _ = group_slots(self.categories())                           # finished slots left the batch
+            dec, pre = groups[StateCategory.FORWARD_ONE_DECODE], groups[StateCategory.FORWARD_ONE_PREFILL]
+            rows = dec + pre
         if not rows:
-            return 0
-        toks = []
-        for p in rows:
-            s = self.slots[p]
-            toks.append([s.pending.pop(0) if s.pending else s.next_token])
-        idx = torch.tensor(rows, dtype=torch.int32, device=self.device)
-        st, el = self._state_for(idx)
-        logits = self.model._step(self.model._tokens(toks), len(rows), 1, st, False, slot_idx=idx)
-        self.batch_state[2][idx.long()] = el
-        sample_rows = [i for i, p in enumerate(rows) if not self.slots[p].pending]    # prompt fully consumed: logits count
-        if sample_rows:
-            sel = logits if len(sample_rows) == len(rows) else logits[torch.tensor(sample_rows, device=logits.device)]
-            new = self._sample([rows[i] for i in sample_rows], sel)
-            for i, tok in zip(sample_rows, new):
-                p = rows[i]
-                s, t = self.slots[p], self.slots[p].task
-                s.next_token = tok
-                s.category = StateCategory.FORWARD_ONE_DECODE
-                t.generated_tokens.append(tok)
-                if t.output_queue is not None:
-                    t.output_queue.put_nowait(("token", tok, self.tokenizer.decode([tok]),
-                                               logits[i].detach().clone() if t.return_logits else None))
-                if tok in t.stop_tokens:
-                    self._finish(p, RequestStatus.FINISHED_STOPPED)
-                elif t.max_tokens is not None and len(t.generated_tokens) >= t.max_tokens:
-                    self._finish(p, RequestStatus.FINISHED_LENGTH_CAPPED)
-        self.steps["decode"] += 1
-        self.steps["decode_tokens"] += len(sample_rows)
+            return len(prev["rows"]) if prev is not None else 0
+        self._inflight = self._launch_decode(rows, None)
+        if not self.pipeline:
+            rec, self._inflight = self._inflight, None
+            self._finish_decode(rec)
         return len(rows)
 
     def _process_events(self) -> None:
@@ -439,7 +528,7 @@ class Worker:
                 time.sleep(0.001)
 
     def busy(self) -> bool:
-        return any(s.category != StateCategory.EMPTY for s in self.slots)
+        return self._inflight is not None or any(s.category != StateCategory.EMPTY for s in self.slots)
 
 
 # ------------------------------------------------------------------------------------------------ asyncio side
