@@ -348,7 +348,8 @@ void gemm_set_debug_buffer(unsigned long long* p) { g_gemm_dbg = p; }
 
 int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* W, long ldw, void* out, long ldo,
                       const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,
-                      cudaStream_t stream, bool pdl) {
+                      cudaStream_t stream, bool pdl, int* defer_splits) {
+    if (defer_splits) *defer_splits = 0;
     if (M < 0 || N <= 0 || K <= 0 || (K & 7) || (N & 7) || (lda & 7) || (ldw & 7) || (ldo & 7)) return B200_ERR_BAD_ARG;
     if (epilogue < B200_EPI_NONE || epilogue > B200_EPI_RESADD) return B200_ERR_BAD_ARG;
     if (epilogue == B200_EPI_RESADD && residual == nullptr) return B200_ERR_BAD_ARG;
@@ -359,7 +360,7 @@ int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* 
     if (M == 0) return 0;
     if (M > 128 && !no_pair()) {  // decode / prefill sized token counts: CTA pairs (gemm_pair.cu)
         LinearDesc d1 = {N, K, A, lda, W, ldw, out, ldo, bias, residual, epilogue};
-        const int rc = pair_group_launch(1, &d1, M, workspace, workspace_bytes, stream, pdl, g_gemm_dbg);
+        const int rc = pair_group_launch(1, &d1, M, workspace, workspace_bytes, stream, pdl, g_gemm_dbg, defer_splits);
         if (rc != B200_ERR_UNSUPPORTED) return rc;
     }
     GemmPlan p = plan_gemm(M, N, K);
@@ -383,6 +384,7 @@ int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* 
     g.kb_per_split = p.kb_per_split;
     g.n_split = p.n_split;
     g.dbg = g_gemm_dbg;
+    g.defer = nullptr;
     if (p.mt == 2)
         return p.bn == 256 ? launch_cfg<2, 256>(p, tmA, tmW, g, stream, pdl)
                : p.bn == 128 ? launch_cfg<2, 128>(p, tmA, tmW, g, stream, pdl) : launch_cfg<2, 32>(p, tmA, tmW, g, stream, pdl);
@@ -469,6 +471,7 @@ int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long
         g.kb_per_split = (kb + s - 1) / s;
         g.n_split = s;
         g.dbg = nullptr;
+        g.defer = nullptr;
         end += (d[i].N + bn - 1) / bn;
         grp.tile_end[i] = end;
     }

@@ -70,7 +70,9 @@ struct GemmArgs {
     int epi;
     float* partials;  // [tile][split][unit][128][32] fp32
     int kb_per_split;
-    int n_split;      // == cluster size along z
+    int n_split;      // == cluster size along z (gridDim.z with cluster z = 1 when `defer` is set)
+    float* defer;     // non-null: K split whose reduction is DEFERRED to the consumer kernel — split z stores its fp32 partial
+                      // tile row-major at defer[(z * M + row) * N + col]; no bias / residual / rounding here (gemm_pair.cu only)
     unsigned long long* dbg;  // optional timeline probe (globaltimer ns), 8 slots per CTA; nullptr in production
 };
 
@@ -139,6 +141,28 @@ DEVI void emit_unit(const float (&v)[32], uint32_t stg, const EpiCtx& c, int row
         const float4 lo = lds128(a), hi = lds128(a + 16u);
         const int row = row0 + r;
         if (row < c.M && col_ok) *reinterpret_cast<uint4*>(c.out + (size_t)row * c.ldo + col) = finish8<EPI>(lo, hi, b8, r8[i]);
+    }
+}
+
+// The same unit stored as raw fp32 (deferred K-split partial): a warp store covers 8 rows x 128 contiguous bytes.
+DEVI void emit_unit_f32(const float (&v)[32], uint32_t stg, float* __restrict__ dst, long ld, int M, int N, int row0, int col0,
+                        int lane) {
+    const int sub_r = lane >> 2, c8 = (lane & 3) * 8;
+    const int col = col0 + c8;
+#pragma unroll
+    for (int e = 0; e < 8; e++) sts128(stg + (uint32_t)(lane * STG_LD + 4 * e) * 4u, v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int r = i * 8 + sub_r;
+        const uint32_t a = stg + (uint32_t)(r * STG_LD + c8) * 4u;
+        const float4 lo = lds128(a), hi = lds128(a + 16u);
+        const int row = row0 + r;
+        if (row < M && col < N) {
+            float4* q = reinterpret_cast<float4*>(dst + (size_t)row * ld + col);
+            __stcg(q, lo);
+            __stcg(q + 1, hi);
+        }
     }
 }
 

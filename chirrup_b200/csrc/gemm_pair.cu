@@ -283,6 +283,22 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
         const uint32_t stg0 = smem_u32(smem) + (uint32_t)q * (2 * 32 * STG_LD * 4);
         if (S == 1) {
             EPI_DISPATCH(epi, epilogue_direct<E>(tmem_base, q, lane, n_valid, ec, m0 + q * 32, n0, stg0));
+        } else if (g.defer) {
+            // deferred reduction: this split's raw fp32 partial, row-major, for the consumer kernel to sum (glue.h)
+            float* dst = g.defer + (size_t)split * g.M * g.N;
+            float va[32], vb[32];
+            tmem_ld_unit(tmem_base, q, 0, va);
+#pragma unroll 1
+            for (int u = 0; u < n_valid; u += 2) {
+                tmem_ld_wait();
+                if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
+                emit_unit_f32(va, stg0, dst, g.N, g.M, g.N, m0 + q * 32, n0 + u * 32, lane);
+                if (u + 1 < n_valid) {
+                    tmem_ld_wait();
+                    if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
+                    emit_unit_f32(vb, stg0 + 32 * STG_LD * 4, dst, g.N, g.M, g.N, m0 + q * 32, n0 + (u + 1) * 32, lane);
+                }
+            }
         } else {
             // park: unit u of (tile, pair rank, split) = 8 column groups x 128 rows x float4, thread-major; the TMEM load of
             // unit u+1 is in flight while unit u is stored
@@ -309,7 +325,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
         }
     }
 
-    if (S > 1) {
+    if (S > 1 && !g.defer) {
         PPROBE(4);
         // every CTA of the cluster (both pair ranks, all K splits of this tile) has parked its partial
         asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy global writes above vs the bulk (async-proxy) reads below
@@ -380,12 +396,12 @@ int pair_slots(int s) {
 }
 
 // Modelled time (us) of one CTA of a (bn, s) plan with kps K-blocks per split (rates: DESIGN.md §3, profiles/r01_gemm_timeline*).
-double pair_cta_cost(int bn, int s, int kps) {
+double pair_cta_cost(int bn, int s, int kps, bool defer = false) {
     const double clk = 1500.0;                                    // MHz under tensor load (power-capped)
     const double mma = 4.0 * (bn / 2.0);                          // cycles per K block: 4 UMMAs of 256 x bn x 16
     const double ingest = (16384.0 + bn * 64.0) / 52.0;           // bytes into this SM per K block at ~52 B/clk
     const double main_us = kps * (mma > ingest ? mma : ingest) / clk;
-    const double epi_us = (s > 1) ? 1.2 + 4.5 * bn / 256.0 : 0.5 + 2.5 * bn / 256.0;
+    const double epi_us = defer ? 0.5 + 3.0 * bn / 256.0 : (s > 1) ? 1.2 + 4.5 * bn / 256.0 : 0.5 + 2.5 * bn / 256.0;
     return 1.8 + main_us + epi_us;
 }
 
@@ -396,7 +412,8 @@ int pair_slots_query(int s) { return (s >= 1 && s <= PAIR_MAX_SPLIT) ? pair_slot
 // Up to PAIR_MAX_GROUP linear layers that share M (> 128) in ONE launch.  Returns B200_ERR_UNSUPPORTED when the group does
 // not fit this kernel (the caller then uses gemm.cu).
 int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream, bool pdl,
-                      unsigned long long* dbg) {
+                      unsigned long long* dbg, int* defer_splits) {
+    if (defer_splits) *defer_splits = 0;
     if (n <= 0 || n > PAIR_MAX_GROUP || M <= 128) return B200_ERR_UNSUPPORTED;
     const int gy = (M + 255) / 256;
     int min_kb = 1 << 30;
@@ -449,6 +466,37 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
             }
         }
     }
+    // Deferred reduction (one residual-add problem, consumer sums the partials): the K split is then over independent CTA
+    // pairs — no cluster along z, so S is not limited by the 15 clusters of 8 the device co-schedules (FFN value: 16 tiles x 4).
+    bool defer = false;
+    static const bool defer_env = getenv("B200_NO_DEFER") == nullptr;
+    if (defer_splits && defer_env && n == 1 && gy == 1 && d[0].epi == B200_EPI_RESADD && !force_bn && !force_s && workspace) {
+        const int kb = (d[0].K + BK - 1) / BK;
+        const int slots = pair_slots(1);
+        const int dc[3] = {256, 192, 128};
+        static const int min_kb_env = getenv("B200_DEFER_MIN_KB") ? atoi(getenv("B200_DEFER_MIN_KB")) : 0;  // tuning overrides
+        static const int force_ds = getenv("B200_DEFER_S") ? atoi(getenv("B200_DEFER_S")) : 0;
+        for (int s = 2; s <= 8 && s <= kb / 2 && kb >= min_kb_env; s++) {
+            if (force_ds && s != force_ds) continue;
+            const int kps = (kb + s - 1) / s;
+            if ((kb + kps - 1) / kps != s) continue;
+            if ((long)s * M * d[0].N * 4 > workspace_bytes) break;
+            for (int ci = 0; ci < 3; ci++) {
+                int bn = dc[ci];
+                const int n32 = (d[0].N + 31) / 32 * 32;
+                if (bn > n32) bn = n32;
+                const long tiles = (long)((d[0].N + bn - 1) / bn) * s;
+                const long waves = (tiles + slots - 1) / slots;
+                const double cost = waves * pair_cta_cost(bn, s, kps, true) + 2.0;  // + the consumer's share
+                if (cost < best_cost) {
+                    best_cost = cost;
+                    best_s = s;
+                    best_bn[0] = bn;
+                    defer = true;
+                }
+            }
+        }
+    }
     const int s = best_s;
     PairGroup grp;
     grp.n = n;
@@ -477,6 +525,7 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
         g.kb_per_split = (kb + s - 1) / s;
         g.n_split = s;
         g.dbg = dbg;
+        g.defer = defer ? static_cast<float*>(workspace) : nullptr;
         end += (d[i].N + bn - 1) / bn;
         P.tile_end = end;
         P.bn = bn;
@@ -485,7 +534,7 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
         grp.p[i].tile_end = end;
         grp.p[i].bn = 32;
     }
-    if (s > 1) {
+    if (s > 1 && !defer) {
         const long need = (long)end * gy * 2 * s * 8 * PAIR_UNIT_FLOATS * 4;
         if (workspace == nullptr || workspace_bytes < need) return B200_ERR_WORKSPACE;
     }
@@ -500,12 +549,14 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = s;
+    attr[0].val.clusterDim.z = defer ? 1 : s;
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 2 : 1;
-    return (int)cudaLaunchKernelEx(&cfg, pair_gemm_kernel, grp);
+    const int rc = (int)cudaLaunchKernelEx(&cfg, pair_gemm_kernel, grp);
+    if (rc == 0 && defer) *defer_splits = s;
+    return rc;
 }
 
 }  // namespace b200

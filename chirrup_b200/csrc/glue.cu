@@ -139,17 +139,18 @@ DEVI H8 layer_norm8_pre(const H8& x, bool active, int C, const int4& wq, const i
 // (last written by this same kernel one step earlier) — is fetched BEFORE griddepcontrol.wait, so under programmatic dependent
 // launch only the x row load and two one-barrier reductions remain on the critical path.
 template <int NMIX>
-__global__ void __launch_bounds__(512) ln_shift_mix_kernel(int T, int C, const __half* __restrict__ x,
+__global__ void __launch_bounds__(512) ln_shift_mix_kernel(int T, int C, __half* __restrict__ x,
                                                             const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
                                                             __half* __restrict__ shift, long shift_stride,
-                                                            const int* __restrict__ slot_idx, MixPtrs<NMIX> mp) {
+                                                            const int* __restrict__ slot_idx, MixPtrs<NMIX> mp,
+                                                            const float* __restrict__ part, int n_part, long part_stride) {
     __shared__ float red[3 * 64];
     pdl_launch_dependents();
     const int m = blockIdx.x;
     const int b = m / T, t = m - b * T;
     const int c0 = threadIdx.x * 8;
     const bool active = c0 < C;
-    const __half* xrow = x + (size_t)m * C;
+    __half* xrow = x + (size_t)m * C;
     __half* srow = shift + (size_t)(slot_idx ? slot_idx[b] : b) * shift_stride;
     // kept packed (8 fp16 per int4) until used: 9 x 4 registers instead of 9 x 8
     const int4 z4 = make_int4(0, 0, 0, 0);
@@ -169,6 +170,35 @@ __global__ void __launch_bounds__(512) ln_shift_mix_kernel(int T, int C, const _
 #pragma unroll
     for (int e = 0; e < 8; e++) xv.f[e] = 0.f;
     if (active) xv = ld8(xrow + c0);
+    if (part != nullptr && active) {
+        // The producing GEMM left its K split unreduced (glue.h, linear_f16_launch defer_splits): finish the residual add here,
+        // x <- fp16(x + fp16(p_0 + p_1 + ...)) in split order — bit for bit what the GEMM's own reduction stores — and write the
+        // row back for the residual stream.  T == 1 only (no CTA reads another CTA's row).
+        const float* pr = part + (size_t)m * C + c0;
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; e++) acc[e] = 0.f;
+#pragma unroll 1
+        for (int z0 = 0; z0 < n_part; z0 += 4) {
+            float4 lo[4], hi[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (z0 + j < n_part) {
+                    const float4* q = reinterpret_cast<const float4*>(pr + (size_t)(z0 + j) * part_stride);
+                    lo[j] = __ldcg(q);
+                    hi[j] = __ldcg(q + 1);
+                }
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (z0 + j < n_part) {
+                    acc[0] += lo[j].x; acc[1] += lo[j].y; acc[2] += lo[j].z; acc[3] += lo[j].w;
+                    acc[4] += hi[j].x; acc[5] += hi[j].y; acc[6] += hi[j].z; acc[7] += hi[j].w;
+                }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; e++) xv.f[e] = hr(xv.f[e] + hr(acc[e]));
+        st8(xrow + c0, xv);
+    }
     const H8 cur = layer_norm8_pre(xv, active, C, ww, bb, red);
     if (t > 0) {
         H8 pv = xv;
@@ -321,19 +351,23 @@ int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __ha
     if (M <= 0) return 0;
     return launch_kernel(embed_gather_kernel, dim3(M), dim3(128), 0, s, pdl, 0, M, C, tokens, emb, x);
 }
-int launch_ln_shift_mix6(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
-                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl) {
+int launch_ln_shift_mix6(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
+                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl, const float* part,
+                         int n_part) {
     if (B * T <= 0) return 0;
     if (C > 4096) return -4;  // B200_ERR_UNSUPPORTED: one thread per 8 channels, 512 threads (every RWKV-7 g1 size has C <= 4096)
+    if (part && (T != 1 || n_part < 1)) return -1;
     return launch_kernel(ln_shift_mix_kernel<6>, dim3(B * T), dim3(ln_threads(C)), 0, s, pdl, 0, T, C, x, ln_w, ln_b, shift,
-                         shift_stride, slot_idx, mp);
+                         shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
 }
-int launch_ln_shift_mix1(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
-                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s, bool pdl) {
+int launch_ln_shift_mix1(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
+                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s, bool pdl, const float* part,
+                         int n_part) {
     if (B * T <= 0) return 0;
     if (C > 4096) return -4;
+    if (part && (T != 1 || n_part < 1)) return -1;
     return launch_kernel(ln_shift_mix_kernel<1>, dim3(B * T), dim3(ln_threads(C)), 0, s, pdl, 0, T, C, x, ln_w, ln_b, shift,
-                         shift_stride, slot_idx, mp);
+                         shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
 }
 int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off, const __half* ln_w, const __half* ln_b,
                    __half* out, cudaStream_t s, bool pdl) {

@@ -13,10 +13,14 @@ struct MixPtrs {
 };
 
 int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __half* x, cudaStream_t s, bool pdl = false);
-int launch_ln_shift_mix6(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
-                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl = false);
-int launch_ln_shift_mix1(int B, int T, int C, const __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
-                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s, bool pdl = false);
+// part != nullptr (T == 1 only): x is first completed in place from the producer's n_part deferred K-split partials
+// (fp32, split stride B*T*C floats; see linear_f16_launch) — x <- fp16(x + fp16(sum of partials in split order)).
+int launch_ln_shift_mix6(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
+                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl = false,
+                         const float* part = nullptr, int n_part = 0);
+int launch_ln_shift_mix1(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
+                         long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s, bool pdl = false,
+                         const float* part = nullptr, int n_part = 0);
 int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off, const __half* ln_w, const __half* ln_b,
                    __half* out, cudaStream_t s, bool pdl = false);
 int launch_add_elapsed(int B, int T, int* elapsed, cudaStream_t s, bool pdl = false);
@@ -56,7 +60,11 @@ int launch_wkv7_seq(int B, int T, int C, int H, void* state, long state_slot_str
 // gemm.cu
 int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* W, long ldw, void* out, long ldo,
                       const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,
-                      cudaStream_t stream, bool pdl = false);
+                      cudaStream_t stream, bool pdl = false, int* defer_splits = nullptr);
+// defer_splits != nullptr (B200_EPI_RESADD only): the launch MAY split K over S = *defer_splits > 0 independent CTA pairs and
+// leave the reduction to the consumer — `out` is then NOT written; split z's fp32 partial of out[row][col] is at
+// ((float*)workspace)[(z * M + row) * N + col] and the consumer computes fp16(residual + round_h(p_0 + p_1 + ... in that order)),
+// exactly what the in-kernel reduction produces.  *defer_splits == 0: the launch completed `out` itself.
 
 struct LinearDesc {
     int N, K;
@@ -77,6 +85,6 @@ int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long
 // gemm_pair.cu: the same, on cta_group::2 CTA pairs (128 < M; up to 8 problems).  Returns B200_ERR_UNSUPPORTED when the group
 // does not fit that kernel.
 int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream, bool pdl,
-                      unsigned long long* dbg = nullptr);
+                      unsigned long long* dbg = nullptr, int* defer_splits = nullptr);
 
 }  // namespace b200

@@ -121,10 +121,16 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
         }                                                                                             \
     } while (0)
     auto lin = [&](long rows, int N, int K, const __half* A, const __half* W, __half* out, const __half* bias,
-                   const __half* res, int epi) {
+                   const __half* res, int epi, int* defer_splits = nullptr) {
         return linear_f16_launch((int)rows, N, K, A, K, W, K, out, N, bias, res, epi, ws.counters_and_partials, ws.lin_bytes, st,
-                                 pdl);
+                                 pdl, defer_splits);
     };
+    // Decode (T == 1): the two residual-add GEMMs (output projection, FFN value) may leave their K split unreduced in the
+    // linear workspace; the LayerNorm/shift/mix kernel that consumes x next finishes the add (glue.h).  The workspace is free
+    // in between: the consumer is always the very next launch.
+    const bool may_defer = T == 1 && getenv("B200_NO_DEFER") == nullptr;
+    const float* partials = reinterpret_cast<const float*>(ws.counters_and_partials);
+    int def_o = 0, def_f = 0;  // pending splits of the output projection / of the previous layer's FFN value
     __half* s0 = static_cast<__half*>(state0);
     __half* s1 = static_cast<__half*>(state1);
 
@@ -138,7 +144,9 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             mp.out[i] = ws.mix[i];
         }
         __half *xr = ws.mix[0], *xw = ws.mix[1], *xk = ws.mix[2], *xv = ws.mix[3], *xa = ws.mix[4], *xg = ws.mix[5];
-        RUN(launch_ln_shift_mix6(B, T, C, ws.x, w[B200_LW_LN1_W], w[B200_LW_LN1_B], s0 + l * s0_layer_stride, C, slot_idx, mp, st, pdl));
+        RUN(launch_ln_shift_mix6(B, T, C, ws.x, w[B200_LW_LN1_W], w[B200_LW_LN1_B], s0 + l * s0_layer_stride, C, slot_idx, mp, st, pdl,
+                                 def_f ? partials : nullptr, def_f));
+        def_f = 0;
         __half* vbuf = (l == 0) ? ws.vfirst : ws.v;  // layer 0: v_first = v (rwkv7.py:636)
         // r, k, v and the four LoRA down-projections read only the six mixes: ONE grouped launch (7 problems; 6 on layer 0, which
         // has no v-gate, rwkv7.py:636), then the four up-projections in another
@@ -198,15 +206,18 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             po.out = ws.yg;
             RUN(launch_tmix_post(po, st, pdl));
         }
-        RUN(lin(M, C, C, ws.yg, w[B200_LW_OUTPUT], ws.x, nullptr, ws.x, B200_EPI_RESADD));
+        RUN(lin(M, C, C, ws.yg, w[B200_LW_OUTPUT], ws.x, nullptr, ws.x, B200_EPI_RESADD, may_defer ? &def_o : nullptr));
         // ---- CMix
         MixPtrs<1> mc;
         mc.mix[0] = w[B200_LW_FFN_X_K];
         mc.out[0] = ws.kx;
         RUN(launch_ln_shift_mix1(B, T, C, ws.x, w[B200_LW_LN2_W], w[B200_LW_LN2_B], s0 + l * s0_layer_stride + s0_which_stride, C,
-                                 slot_idx, mc, st, pdl));
+                                 slot_idx, mc, st, pdl, def_o ? partials : nullptr, def_o));
+        def_o = 0;
         RUN(lin(M, F, C, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, nullptr, nullptr, B200_EPI_RELU_SQ));
-        RUN(lin(M, C, F, ws.hidden, w[B200_LW_FFN_VALUE], ws.x, nullptr, ws.x, B200_EPI_RESADD));
+        // the last layer's x goes to ln_out, which takes finished rows
+        RUN(lin(M, C, F, ws.hidden, w[B200_LW_FFN_VALUE], ws.x, nullptr, ws.x, B200_EPI_RESADD,
+                (may_defer && l + 1 < L) ? &def_f : nullptr));
     }
     if (logits) {
         if (full_output) {

@@ -118,7 +118,8 @@ def bound(tol, self_noise):
 
 
 @needs_ref
-@pytest.mark.parametrize("geom_name,B,P,D,n_layer", [("small", 5, 7, 6, None), ("0.1B", 8, 12, 6, None), ("1.5B", 64, 3, 4, None)])
+@pytest.mark.parametrize("geom_name,B,P,D,n_layer", [("small", 5, 7, 6, None), ("0.1B", 8, 12, 6, None), ("1.5B", 64, 3, 4, None),
+                                                      ("0.1B", 200, 3, 4, None), ("1.5B", 256, 2, 3, 6)])
 def test_model_matches_oracle_on_gpu_parity_bar(geom_name, B, P, D, n_layer):
     """BASELINE.json configs[1] (1.5B: L24, D2048, fp16, bsz 64) and smaller geometries, trained_like checkpoint: logits, all
     three state tensors and every greedy token vs the oracle running torch/cuBLAS + the reference's CUDA WKV kernel.
@@ -300,3 +301,33 @@ def test_fused_tmix_core_equals_three_kernel_chain():
     assert torch.equal(ta, tb) and torch.equal(ea, eb)
     assert rel(la, lb) <= 2e-3 and rel_l2(sa[1], sb[1]) <= 5e-4
     assert torch.count_nonzero(sa[1][:, 1]) == 0 and torch.count_nonzero(sa[1][:, 3]) == 0   # untouched slots stay zero
+
+
+def test_deferred_split_k_reduction_equals_in_kernel_reduction():
+    """Decode with 128 < B <= 256 rows: the output projection and the FFN value GEMM leave their K split unreduced and the next
+    LayerNorm/shift/mix kernel finishes the residual add (csrc/glue.h).  Against the same step with the reduction inside the
+    GEMM (B200_NO_DEFER=1): only the K split points differ, so logits / states agree to fp16 rounding noise and the greedy
+    tokens are identical."""
+    geom, raw, m = build("0.1B", seed=14, recipe="trained_like", n_layer=4)
+    B = 192
+    toks = torch.randint(1, geom.vocab_size, (B, 5), generator=torch.Generator().manual_seed(9)).tolist()
+    outs = {}
+    for mode in ("defer", "in_kernel"):
+        if mode == "in_kernel":
+            os.environ["B200_NO_DEFER"] = "1"
+        else:
+            os.environ.pop("B200_NO_DEFER", None)
+        try:
+            st = m.generate_zero_state(B)
+            lg = m.forward_seq_batch_seperate(toks, st)
+            seq = []
+            for _ in range(6):
+                nxt = lg.float().argmax(-1)
+                seq.append(nxt.clone())
+                lg = m.forward_seq_batch_seperate([[int(t)] for t in nxt], st)
+            outs[mode] = (lg, st, torch.stack(seq))
+        finally:
+            os.environ.pop("B200_NO_DEFER", None)
+    (la, sa, ta), (lb, sb, tb) = outs["defer"], outs["in_kernel"]
+    assert torch.equal(ta, tb) and torch.equal(sa[2], sb[2])
+    assert rel(la, lb) <= 2e-3 and rel_l2(sa[1], sb[1]) <= 5e-4 and rel_l2(sa[0], sb[0]) <= 5e-4
