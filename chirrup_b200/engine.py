@@ -170,6 +170,7 @@ class Worker:
         self._par_dirty = False
         self._inflight: Optional[Dict[str, Any]] = None       # decode step launched, host side not yet done
         self._rows_cache = None
+        self._step_bufs = None
         self.pipeline = True
         self.sample_seed = 0x5EED0000 + sum(map(ord, str(worker_id)))
         self._stop = False
@@ -400,11 +401,20 @@ class Worker:
                 both = torch.tensor([src, host], dtype=torch.int32).to(self.device, non_blocking=True)
                 tok_dev = torch.where(both[0] >= 0, ids_prev[both[0].clamp(min=0).long()], both[1]).contiguous()
         if self._rows_cache is None or self._rows_cache[0] != rows:
-            self._rows_cache = (list(rows), torch.tensor(rows, dtype=torch.int32, device=self.device))
-        idx = self._rows_cache[1]
-        st, el = self._state_for(idx)
-        logits = self.model._step(tok_dev, n, 1, st, False, slot_idx=idx)
-        self.batch_state[2][idx.long()] = el
+            idx = torch.tensor(rows, dtype=torch.int32, device=self.device)
+            self._rows_cache = (list(rows), idx, idx.long())
+        idx, idx_long = self._rows_cache[1], self._rows_cache[2]
+        # fixed input / output buffers: the same addresses every step, so the model replays the step from a CUDA graph
+        if self._step_bufs is None:
+            cap, V = len(self.slots), self.model.vocab_size
+            self._step_bufs = (torch.empty((cap,), dtype=torch.int32, device=self.device),
+                               torch.empty((cap,), dtype=torch.int32, device=self.device),
+                               torch.empty((cap, V), dtype=torch.float16, device=self.device))
+        tok_in, el, out = self._step_bufs[0][:n], self._step_bufs[1][:n], self._step_bufs[2][:n]
+        tok_in.copy_(tok_dev.view(-1))
+        torch.index_select(self.batch_state[2], 0, idx_long, out=el)
+        logits = self.model._step(tok_in, n, 1, [self.batch_state[0], self.batch_state[1], el], False, slot_idx=idx, out=out)
+        self.batch_state[2][idx_long] = el
         sample_rows = [i for i, p in enumerate(rows) if not self.slots[p].pending]    # prompt fully consumed: logits count
         rec: Dict[str, Any] = {"rows": list(rows), "tasks": [self.slots[p].task for p in rows], "sample_rows": sample_rows,
                                "ids": None, "host": None, "event": None, "logits": None}

@@ -51,6 +51,7 @@ class ToyModel:
     def __init__(self, V=50, L=2, C=8):
         self.device = torch.device("cpu")
         self.V, self.L, self.C = V, L, C
+        self.vocab_size = V
         self.calls = []
 
     def generate_zero_state(self, bsz):
