@@ -433,8 +433,8 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
     double best_cost = 1e30;
     const int cands[4] = {force_bn ? force_bn : 256, 192, 128, 64};
     for (int s = 1; s <= PAIR_MAX_SPLIT; s++) {
-        if (s > 1 && (gy > 1 || s > min_kb / 2)) break;
-        if (force_s && s != force_s && force_s <= min_kb / 2 && gy == 1) continue;
+        if (s > 1 && s > min_kb / 2) break;
+        if (force_s && s != force_s && force_s <= min_kb / 2) continue;
         bool ok = true;
         for (int i = 0; i < n && ok; i++) {
             const int kb = (d[i].K + BK - 1) / BK, kps = (kb + s - 1) / s;
@@ -457,6 +457,7 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
                 if (c > worst) worst = c;
             }
             tiles *= gy;
+            if (s > 1 && (workspace == nullptr || tiles * 2 * s * 8 * PAIR_UNIT_FLOATS * 4 > workspace_bytes)) continue;
             const long waves = (tiles + slots - 1) / slots;
             const double cost = waves * worst;
             if (cost < best_cost) {

@@ -244,3 +244,11 @@ extern "C" int b200_argmax_f16(int rows, int V, const void* logits, long ld, int
     if (rows < 0 || V <= 0 || (V & 7) || (ld & 7)) return B200_ERR_BAD_ARG;
     return launch_argmax_rows(rows, V, static_cast<const __half*>(logits), ld, out, static_cast<cudaStream_t>(stream));
 }
+
+extern "C" int b200_slot_copy(void* dst, long dst_pitch, const void* src, long src_pitch, long width_bytes, long rows,
+                              void* stream) {
+    if (!dst || !src || width_bytes < 0 || rows < 0 || dst_pitch < width_bytes || src_pitch < width_bytes) return B200_ERR_BAD_ARG;
+    if (width_bytes == 0 || rows == 0) return 0;
+    return (int)cudaMemcpy2DAsync(dst, (size_t)dst_pitch, src, (size_t)src_pitch, (size_t)width_bytes, (size_t)rows,
+                                  cudaMemcpyDefault, static_cast<cudaStream_t>(stream));
+}

@@ -41,17 +41,59 @@ def clear_slot(state: List[torch.Tensor], slot: int) -> None:
     state[2][slot] = 0
 
 
+_peers_enabled = set()
+
+
+def _enable_peer(a: torch.device, b: torch.device) -> None:
+    """torch turns peer access on the first time it copies between two GPUs; do that once per pair so that the strided DMA
+    copies below go over NVLink instead of being staged through host memory by the driver."""
+    key = (a.index, b.index)
+    if key in _peers_enabled:
+        return
+    torch.zeros(1, device=a).to(b)
+    torch.zeros(1, device=b).to(a)
+    _peers_enabled.add(key)
+    _peers_enabled.add((b.index, a.index))
+
+
+def _rows_view(t: torch.Tensor):
+    """(pointer, pitch bytes, width bytes, rows) of a view that is `rows` contiguous pieces at one pitch, else None."""
+    if t.dim() < 2 or t.dtype != torch.float16:
+        return None
+    # state[1][:, s]: (L, H, 64, 64), inner block contiguous; state[0][:, :, s]: (L, 2, C), rows (l, which) at a uniform pitch
+    if t.dim() == 4 and t[0].is_contiguous():
+        return t.data_ptr(), t.stride(0) * 2, t[0].numel() * 2, t.shape[0]
+    if t.dim() == 3 and t.stride(2) == 1 and t.stride(0) == 2 * t.stride(1) and t.shape[1] == 2:
+        return t.data_ptr(), t.stride(1) * 2, t.shape[2] * 2, 2 * t.shape[0]
+    return None
+
+
+def _copy_rows(dst: torch.Tensor, src: torch.Tensor) -> None:
+    """dst <- src for one slot's rows: one strided DMA copy (``b200_slot_copy``) on the current stream of dst's device when both
+    are CUDA views with the slot-table layout, else a torch copy (host tiers)."""
+    dv, sv = _rows_view(dst), _rows_view(src)
+    if dst.is_cuda and src.is_cuda and dv and sv and dv[2:] == sv[2:]:
+        from . import _lib
+        _lib.check(_lib.lib().b200_slot_copy(dv[0], dv[1], sv[0], sv[1], dv[2], dv[3],
+                                             torch.cuda.current_stream(dst.device).cuda_stream), "b200_slot_copy")
+    else:
+        dst.copy_(src, non_blocking=True)
+
+
 def migrate_slot(src: List[torch.Tensor], src_slot: int, dst: List[torch.Tensor], dst_slot: int) -> int:
-    """Move one request's state between two workers' slot tables (possibly on different GPUs) with strided device-to-device
-    copies; returns the bytes moved.  Ordered on the destination's current stream after the source's current stream."""
+    """Move one request's state between two workers' slot tables (possibly on different GPUs): two strided DMA copies
+    (``b200_slot_copy``: the L WKV tiles, the 2L shift rows) + the elapsed counter, device to device — over NVLink between
+    peers, never through host memory, no SM work.  Returns the bytes moved.  Ordered on the destination's current stream after
+    the source's current stream."""
     sdev, ddev = src[0].device, dst[0].device
     if sdev != ddev and sdev.type == "cuda" and ddev.type == "cuda":
+        _enable_peer(sdev, ddev)
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(sdev))
         torch.cuda.current_stream(ddev).wait_event(ev)
     with torch.cuda.device(ddev) if ddev.type == "cuda" else _Null():
-        dst[0][:, :, dst_slot].copy_(src[0][:, :, src_slot], non_blocking=True)
-        dst[1][:, dst_slot].copy_(src[1][:, src_slot], non_blocking=True)
+        _copy_rows(dst[0][:, :, dst_slot], src[0][:, :, src_slot])
+        _copy_rows(dst[1][:, dst_slot], src[1][:, src_slot])
         dst[2][dst_slot:dst_slot + 1].copy_(src[2][src_slot:src_slot + 1], non_blocking=True)
     return slot_bytes(src)
 

@@ -201,6 +201,14 @@ typedef struct b200_sample_params {
 } b200_sample_params;
 int b200_sample_f16(int rows, int V, void* logits, long ld, const b200_sample_params* params, int* out, void* stream);
 
+/* One request's state rows in or out of a slot table (admission, cache extraction, migration between workers): `rows`
+ * pieces of `width_bytes` at pitches dst_pitch / src_pitch bytes, as ONE strided DMA copy on `stream` — device to device on
+ * one GPU, between peer GPUs (NVLink when peer access is enabled), or to / from pinned host memory.  No SM work, so it runs
+ * under a decode step.  Replaces the host round trips and the three-copy slot swap of chirrup/worker.py:427-429, :468-470
+ * (slot -> CPU), :586-597 (CPU -> slot), :304-360 (swap).  state[1] of slot s: dst = base + s*H*64*64*2, pitch =
+ * n_slots*H*64*64*2, width = H*64*64*2, rows = L;  state[0]: pitch = n_slots*C*2, width = C*2, rows = 2L. */
+int b200_slot_copy(void* dst, long dst_pitch, const void* src, long src_pitch, long width_bytes, long rows, void* stream);
+
 /* Number of kernels the last b200_model_forward on this model launched (bench.py reports it as gpu_launches). */
 int b200_model_last_launch_count(const b200_model* m);
 

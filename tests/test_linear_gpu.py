@@ -89,7 +89,8 @@ def test_linear_group_tmix_shapes(M):
         assert torch.allclose(y.float(), ref.float(), rtol=3e-3, atol=3e-3), (K, e, (y.float() - ref.float()).abs().max().item())
 
 
-@pytest.mark.parametrize("M,N,K", [(256, 4096, 16384), (256, 512, 512), (255, 264, 4096), (1024, 1024, 1024)])
+@pytest.mark.parametrize("M,N,K", [(256, 4096, 16384), (256, 512, 512), (255, 264, 4096), (1024, 1024, 1024),
+                                   (512, 4096, 16384), (500, 4096, 4096), (768, 1024, 8192)])
 def test_linear_pair_splitk_and_tails(M, N, K):
     """CTA-pair kernel: K split over the cluster (deterministic thread-major partials), N / M tails, several M blocks."""
     from chirrup_b200 import ops
