@@ -119,7 +119,7 @@ def bound(tol, self_noise):
 
 @needs_ref
 @pytest.mark.parametrize("geom_name,B,P,D,n_layer", [("small", 5, 7, 6, None), ("0.1B", 8, 12, 6, None), ("1.5B", 64, 3, 4, None),
-                                                      ("0.1B", 200, 3, 4, None), ("1.5B", 256, 2, 3, 6)])
+                                                      ("0.1B", 200, 3, 4, None), ("1.5B", 256, 2, 3, 6), ("7.2B", 256, 2, 3, 2)])
 def test_model_matches_oracle_on_gpu_parity_bar(geom_name, B, P, D, n_layer):
     """BASELINE.json configs[1] (1.5B: L24, D2048, fp16, bsz 64) and smaller geometries, trained_like checkpoint: logits, all
     three state tensors and every greedy token vs the oracle running torch/cuBLAS + the reference's CUDA WKV kernel.
@@ -331,3 +331,51 @@ def test_deferred_split_k_reduction_equals_in_kernel_reduction():
     (la, sa, ta), (lb, sb, tb) = outs["defer"], outs["in_kernel"]
     assert torch.equal(ta, tb) and torch.equal(sa[2], sb[2])
     assert rel(la, lb) <= 2e-3 and rel_l2(sa[1], sb[1]) <= 5e-4 and rel_l2(sa[0], sb[0]) <= 5e-4
+
+
+def test_headline_configuration_properties_7p2B_bsz256():
+    """BASELINE.json configs[2] at full size (7.2B: L32, C4096, 256 decode rows; the oracle cannot run this in seconds):
+    size-independent properties of the step.  (1) Two evaluations from equal states are bit-identical (no atomics, fixed split
+    order).  (2) Rows are independent and position-free: permuting the batch rows AND addressing the state through the
+    matching slot permutation permutes the logits rows bit for bit and leaves every state slot bit-identical.  (3) elapsed
+    advances by exactly T per row; untouched spare slots stay zero.  (4) The graph-replayed step equals the eagerly launched one."""
+    from chirrup_b200.rwkv7 import RWKV_x070, make_args
+
+    geom = GEOMETRIES["7.2B"]
+    raw = make_checkpoint(geom, seed=3, recipe="trained_like", device="cuda", dtype=torch.float16)
+    m = RWKV_x070(make_args(), state_dict=raw)
+    del raw
+    B, V = 256, geom.vocab_size
+    g = torch.Generator().manual_seed(11)
+    prompt = torch.randint(1, V, (B, 4), generator=g)
+    base = m.generate_zero_state(B + 3)
+    ident = torch.arange(B, dtype=torch.int32, device="cuda")
+    el0 = torch.zeros(B, dtype=torch.int32, device="cuda")
+    m._step(m._tokens(prompt), B, 4, [base[0], base[1], el0], False, want_logits=False, slot_idx=ident)
+    tok = torch.randint(1, V, (B,), generator=g).to(torch.int32).cuda()
+    perm = torch.randperm(B, generator=g).cuda()
+
+    def run(order, graph):
+        st = [base[0].clone(), base[1].clone()]
+        el = el0[order].contiguous()
+        m.graph_decode = graph
+        lg, tk, oi = None, tok[order].contiguous(), order.to(torch.int32)
+        for _ in range(14 if graph else 2):          # past the capture threshold when graphs are on
+            st[0].copy_(base[0]); st[1].copy_(base[1]); el.copy_(el0[order])
+            lg = m._step(tk, B, 1, [st[0], st[1], el], False, slot_idx=oi, out=run.out)
+        torch.cuda.synchronize()
+        return lg.clone(), st, el.clone()
+
+    run.out = torch.empty((B, V), dtype=torch.float16, device="cuda")
+    la, sa, ea = run(ident.long(), False)
+    lb, sb, eb = run(ident.long(), False)
+    assert torch.equal(la, lb) and torch.equal(sa[1], sb[1]) and torch.equal(sa[0], sb[0])            # (1)
+    lp, sp, ep = run(perm, False)
+    assert torch.equal(lp, la[perm]) and torch.equal(sp[1], sa[1]) and torch.equal(sp[0], sa[0])      # (2)
+    assert torch.equal(ea, el0 + 1) and torch.equal(ep, (el0 + 1)[perm])                              # (3)
+    assert torch.count_nonzero(sa[1][:, B:]) == 0 and torch.count_nonzero(sa[0][:, :, B:]) == 0
+    assert not torch.equal(sa[1][:, :B], base[1][:, :B])
+    lgr, sg, eg = run(ident.long(), True)
+    assert len(m._graphs) >= 1
+    assert torch.equal(lgr, la) and torch.equal(sg[1], sa[1]) and torch.equal(eg, ea)                 # (4)
+    assert torch.isfinite(la.float()).all()
