@@ -70,7 +70,7 @@ def lib() -> ctypes.CDLL:
             from . import build as _build
 
             _build.build()  # no-op when the in-tree library is newer than its sources
-        L = ctypes.CDLL(LIB_PATH)
+        L = ctypes.CDLL(os.environ.get("CHIRRUP_B200_LIB") or LIB_PATH)  # override: A/B of two builds on one box
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(L, name)  # AttributeError if the library does not export a declared symbol
             fn.restype = res

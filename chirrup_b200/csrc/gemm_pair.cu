@@ -237,15 +237,19 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
             for (int it = 0; it < npre; it++)
                 tma_load_2d_pair(smem + it * PAIR_STAGE_BYTES, &P.tmA, (kb0 + it) * BK, m0,
                                  mapa_shared(smem_u32(&full_bar[it]), leader), pol_a);
+            int s = npre % n_stages;  // running (stage, phase) instead of a division per K block
+            uint32_t ph = (uint32_t)(npre / n_stages) & 1;
             for (int it = npre; it < n_kb; it++) {
-                const int s = it % n_stages;
-                const uint32_t ph = (it / n_stages) & 1;
                 mbar_wait(&empty_bar[s], ph ^ 1);
                 uint8_t* st = smem + s * PAIR_STAGE_BYTES;
                 if (pr == 0) mbar_arrive_expect_tx(&full_bar[s], tx);
                 const uint32_t bar = mapa_shared(smem_u32(&full_bar[s]), leader);
                 tma_load_2d_pair(st, &P.tmA, (kb0 + it) * BK, m0, bar, pol_a);
                 tma_load_2d_pair(st + 128 * BK * 2, &P.tmW, (kb0 + it) * BK, n0 + pr * (bn >> 1), bar, pol_w);
+                if (++s == n_stages) {
+                    s = 0;
+                    ph ^= 1;
+                }
             }
         } else {
             pdl_wait();
@@ -256,10 +260,13 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
         if (pr == 0 && lane == 0) {
             const uint32_t idesc = umma_idesc_f16(256, (uint32_t)bn);
             const uint16_t mask = (uint16_t)(3u << (crank & ~1u));
+            long long t_wait = 0, t_issue = 0, t_mma = 0;  // debug probe only: cycles this thread waits for data / spends issuing
+            int s = 0;
+            uint32_t ph = 0;
             for (int it = 0; it < n_kb; it++) {
-                const int s = it % n_stages;
-                const uint32_t ph = (it / n_stages) & 1;
+                const long long c0 = g.dbg ? clock64() : 0;
                 mbar_wait(&full_bar[s], ph);
+                const long long c1 = g.dbg ? clock64() : 0;
                 if (it == 0) PPROBE(2);
                 tc_fence_after();
                 const uint32_t st = smem_u32(smem + s * PAIR_STAGE_BYTES);
@@ -268,8 +275,23 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
 #pragma unroll
                 for (int k = 0; k < BK / 16; k++)
                     umma_f16_ss_pair(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                const long long c2 = g.dbg ? clock64() : 0;
                 umma_commit_pair(&empty_bar[s], mask);  // frees the stage in both CTAs once these MMAs have read it
+                if (g.dbg && it > 0) {
+                    t_wait += c1 - c0;
+                    t_issue += clock64() - c1;
+                    t_mma += c2 - c1;
+                }
+                if (++s == n_stages) {
+                    s = 0;
+                    ph ^= 1;
+                }
             }
+            if (g.dbg)
+                g.dbg[((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + 7] =
+                    ((unsigned long long)t_wait << 32) | (unsigned long long)(t_issue & 0xffffffffll);
+            if (g.dbg)  // the peer CTA's slot 7 is free: the share of `issue` spent on the four tcgen05.mma alone
+                g.dbg[((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x + 1) * 8 + 7] = (unsigned long long)t_mma;
             umma_commit_pair(accum_bar, mask);  // accumulators complete (both CTAs)
         }
         __syncwarp();

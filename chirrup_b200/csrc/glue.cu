@@ -85,12 +85,13 @@ DEVI H8 layer_norm8(const H8& x, bool active, int C, const __half* w, const __ha
     return o;
 }
 
-__global__ void embed_gather_kernel(int M, int C, const int* __restrict__ tokens, const __half* __restrict__ emb,
+__global__ void embed_gather_kernel(int M, int C, int V, const int* __restrict__ tokens, const __half* __restrict__ emb,
                                     __half* __restrict__ x) {
     pdl_launch_dependents();
     pdl_wait();
     const int m = blockIdx.x;
-    const __half* src = emb + (size_t)tokens[m] * C;
+    const int tok = min(max(tokens[m], 0), V - 1);  // an id outside the vocabulary must not become a wild read
+    const __half* src = emb + (size_t)tok * C;
     __half* dst = x + (size_t)m * C;
     for (int c = threadIdx.x * 8; c < C; c += blockDim.x * 8)
         *reinterpret_cast<int4*>(dst + c) = __ldg(reinterpret_cast<const int4*>(src + c));
@@ -347,9 +348,9 @@ int ln_threads(int C) {
 
 }  // namespace
 
-int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __half* x, cudaStream_t s, bool pdl) {
+int launch_embed_gather(int M, int C, int V, const int* tokens, const __half* emb, __half* x, cudaStream_t s, bool pdl) {
     if (M <= 0) return 0;
-    return launch_kernel(embed_gather_kernel, dim3(M), dim3(128), 0, s, pdl, 0, M, C, tokens, emb, x);
+    return launch_kernel(embed_gather_kernel, dim3(M), dim3(128), 0, s, pdl, 0, M, C, V, tokens, emb, x);
 }
 int launch_ln_shift_mix6(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
                          long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl, const float* part,

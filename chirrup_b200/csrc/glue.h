@@ -12,7 +12,7 @@ struct MixPtrs {
     __half* out[NMIX];        // outputs (M, C)
 };
 
-int launch_embed_gather(int M, int C, const int* tokens, const __half* emb, __half* x, cudaStream_t s, bool pdl = false);
+int launch_embed_gather(int M, int C, int V, const int* tokens, const __half* emb, __half* x, cudaStream_t s, bool pdl = false);
 // part != nullptr (T == 1 only): x is first completed in place from the producer's n_part deferred K-split partials
 // (fp32, split stride B*T*C floats; see linear_f16_launch) — x <- fp16(x + fp16(sum of partials in split order)).
 int launch_ln_shift_mix6(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,

@@ -120,6 +120,14 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             return rc;                                                                                \
         }                                                                                             \
     } while (0)
+    // Timing aid (results are garbage): B200_DEBUG_SKIP is a bit mask of launches to leave out, so that the in-graph marginal cost
+    // of each kernel of the layer can be read off the step time (tools/knockout.sh): 1 ln_shift_mix6, 2 r/k/v + LoRA-down group,
+    // 4 LoRA-up group, 8 fused WKV, 16 output projection, 32 ln_shift_mix1, 64 FFN key, 128 FFN value, 256 ln_out + head.
+    const int skip = getenv("B200_DEBUG_SKIP") ? atoi(getenv("B200_DEBUG_SKIP")) : 0;
+#define RUN_T(tag, call)            \
+    do {                            \
+        if (!(skip & (tag))) RUN(call); \
+    } while (0)
     auto lin = [&](long rows, int N, int K, const __half* A, const __half* W, __half* out, const __half* bias,
                    const __half* res, int epi, int* defer_splits = nullptr) {
         return linear_f16_launch((int)rows, N, K, A, K, W, K, out, N, bias, res, epi, ws.counters_and_partials, ws.lin_bytes, st,
@@ -134,7 +142,7 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
     __half* s0 = static_cast<__half*>(state0);
     __half* s1 = static_cast<__half*>(state1);
 
-    RUN(launch_embed_gather((int)M, C, tokens, m->gw[0], ws.x, st, /*pdl=*/false));
+    RUN(launch_embed_gather((int)M, C, m->V, tokens, m->gw[0], ws.x, st, /*pdl=*/false));
     for (int l = 0; l < L; l++) {
         const __half** w = m->lw + (size_t)l * B200_LW_COUNT;
         // ---- TMix
@@ -144,7 +152,7 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             mp.out[i] = ws.mix[i];
         }
         __half *xr = ws.mix[0], *xw = ws.mix[1], *xk = ws.mix[2], *xv = ws.mix[3], *xa = ws.mix[4], *xg = ws.mix[5];
-        RUN(launch_ln_shift_mix6(B, T, C, ws.x, w[B200_LW_LN1_W], w[B200_LW_LN1_B], s0 + l * s0_layer_stride, C, slot_idx, mp, st, pdl,
+        RUN_T(1, launch_ln_shift_mix6(B, T, C, ws.x, w[B200_LW_LN1_W], w[B200_LW_LN1_B], s0 + l * s0_layer_stride, C, slot_idx, mp, st, pdl,
                                  def_f ? partials : nullptr, def_f));
         def_f = 0;
         __half* vbuf = (l == 0) ? ws.vfirst : ws.v;  // layer 0: v_first = v (rwkv7.py:636)
@@ -162,7 +170,7 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
                 {m->d_g, C, xg, C, w[B200_LW_G1], C, ws.lora[2], m->d_g, nullptr, nullptr, B200_EPI_SIGMOID},
                 {m->d_v, C, xv, C, w[B200_LW_V1], C, ws.lora[3], m->d_v, nullptr, nullptr, B200_EPI_NONE}};
             if (M > 128 && !no_group) {
-                RUN(linear_group_launch(3 + nl, dn, (int)M, ws.counters_and_partials, ws.lin_bytes, st, pdl));
+                RUN_T(2, linear_group_launch(3 + nl, dn, (int)M, ws.counters_and_partials, ws.lin_bytes, st, pdl));
             } else {
                 for (int i = 0; i < 3; i++)
                     RUN(linear_f16_launch((int)M, dn[i].N, dn[i].K, dn[i].A, dn[i].lda, dn[i].W, dn[i].ldw, dn[i].out, dn[i].ldo,
@@ -174,7 +182,7 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
                 {C, m->d_a, ws.lora[1], m->d_a, w[B200_LW_A2], m->d_a, ws.a, C, w[B200_LW_A0], nullptr, B200_EPI_SIGMOID},
                 {C, m->d_g, ws.lora[2], m->d_g, w[B200_LW_G2], m->d_g, ws.g, C, nullptr, nullptr, B200_EPI_NONE},
                 {C, m->d_v, ws.lora[3], m->d_v, w[B200_LW_V2], m->d_v, ws.vg, C, w[B200_LW_V0], nullptr, B200_EPI_SIGMOID}};
-            RUN(linear_group_launch(nl, up, (int)M, ws.counters_and_partials, ws.lin_bytes, st, pdl));
+            RUN_T(4, linear_group_launch(nl, up, (int)M, ws.counters_and_partials, ws.lin_bytes, st, pdl));
         }
         if (!unfused_tmix) {
             // prep + WKV-7 + GroupNorm/bonus/gate in one kernel per (sequence, head) tile
@@ -186,7 +194,7 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             fa.k_k = w[B200_LW_K_K]; fa.k_a = w[B200_LW_K_A]; fa.r_k = w[B200_LW_R_K];
             fa.ln_w = w[B200_LW_LNX_W]; fa.ln_b = w[B200_LW_LNX_B];
             fa.out = ws.yg; fa.elapsed_t = elapsed; fa.slot_idx = slot_idx;
-            RUN(launch_wkv7_fused(fa, s1 + l * s1_layer_stride, (long)C * 64, n_slots, st, pdl));
+            RUN_T(8, launch_wkv7_fused(fa, s1 + l * s1_layer_stride, (long)C * 64, n_slots, st, pdl));
         } else {
             TmixPrepArgs pa;
             pa.M = (int)M; pa.C = C;
@@ -206,29 +214,30 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             po.out = ws.yg;
             RUN(launch_tmix_post(po, st, pdl));
         }
-        RUN(lin(M, C, C, ws.yg, w[B200_LW_OUTPUT], ws.x, nullptr, ws.x, B200_EPI_RESADD, may_defer ? &def_o : nullptr));
+        RUN_T(16, lin(M, C, C, ws.yg, w[B200_LW_OUTPUT], ws.x, nullptr, ws.x, B200_EPI_RESADD, may_defer ? &def_o : nullptr));
         // ---- CMix
         MixPtrs<1> mc;
         mc.mix[0] = w[B200_LW_FFN_X_K];
         mc.out[0] = ws.kx;
-        RUN(launch_ln_shift_mix1(B, T, C, ws.x, w[B200_LW_LN2_W], w[B200_LW_LN2_B], s0 + l * s0_layer_stride + s0_which_stride, C,
+        RUN_T(32, launch_ln_shift_mix1(B, T, C, ws.x, w[B200_LW_LN2_W], w[B200_LW_LN2_B], s0 + l * s0_layer_stride + s0_which_stride, C,
                                  slot_idx, mc, st, pdl, def_o ? partials : nullptr, def_o));
         def_o = 0;
-        RUN(lin(M, F, C, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, nullptr, nullptr, B200_EPI_RELU_SQ));
+        RUN_T(64, lin(M, F, C, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, nullptr, nullptr, B200_EPI_RELU_SQ));
         // the last layer's x goes to ln_out, which takes finished rows
-        RUN(lin(M, C, F, ws.hidden, w[B200_LW_FFN_VALUE], ws.x, nullptr, ws.x, B200_EPI_RESADD,
-                (may_defer && l + 1 < L) ? &def_f : nullptr));
+        RUN_T(128, lin(M, C, F, ws.hidden, w[B200_LW_FFN_VALUE], ws.x, nullptr, ws.x, B200_EPI_RESADD,
+                      (may_defer && l + 1 < L) ? &def_f : nullptr));
     }
     if (logits) {
         if (full_output) {
             RUN(launch_ln_rows((int)M, C, ws.x, 1, 0, m->gw[1], m->gw[2], ws.xo, st, pdl));
             RUN(lin(M, m->V, C, ws.xo, m->gw[3], static_cast<__half*>(logits), nullptr, nullptr, B200_EPI_NONE));
         } else {
-            RUN(launch_ln_rows(B, C, ws.x, T, T - 1, m->gw[1], m->gw[2], ws.xo, st, pdl));
-            RUN(lin(B, m->V, C, ws.xo, m->gw[3], static_cast<__half*>(logits), nullptr, nullptr, B200_EPI_NONE));
+            RUN_T(256, launch_ln_rows(B, C, ws.x, T, T - 1, m->gw[1], m->gw[2], ws.xo, st, pdl));
+            RUN_T(256, lin(B, m->V, C, ws.xo, m->gw[3], static_cast<__half*>(logits), nullptr, nullptr, B200_EPI_NONE));
         }
     }
     RUN(launch_add_elapsed(B, T, elapsed, st, pdl));
+#undef RUN_T
 #undef RUN
     m->last_launches = n;
     return 0;

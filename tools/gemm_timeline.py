@@ -26,3 +26,11 @@ for (M, N, K, epi) in [(256, 4096, 4096, 0), (256, 4096, 16384, 4), (256, 16384,
     for i, n in enumerate(names):
         col = (t[:, i][t[:, i] > 0] - t0).float()
         if len(col): print(f"   {n:14s} min {col.min()/1e3:7.2f} med {col.median()/1e3:7.2f} max {col.max()/1e3:7.2f} us")
+    w = t[:, 7][t[:, 7] >= (1 << 32)]
+    mm = t[:, 7][(t[:, 7] > 0) & (t[:, 7] < (1 << 32))]
+    if len(mm): print(f"   mma thread: of the issue cycles, the four tcgen05.mma alone {mm.float().median():.0f} cyc")
+    if len(w):   # MMA-issuing thread of each leader CTA: cycles waiting for a full stage / issuing the 4 MMAs + commit, per K block
+        kb = (K + 63) // 64
+        wait, issue = (w >> 32).float(), (w & 0xffffffff).float()
+        print(f"   mma thread: wait-for-data {wait.median():.0f} cyc, issue {issue.median():.0f} cyc in total over its K blocks "
+              f"(K blocks per CTA <= {kb}); per-launch medians")
