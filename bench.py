@@ -56,7 +56,7 @@ class ClockSampler:
     """Samples SM clock and throttle reasons through NVML while the timed region runs."""
 
     def __init__(self, index: int):
-        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.samples, self.reasons, self.max_mhz, self.power_w, self.power_limit_w = [], set(), None, [], None
         self._stop = threading.Event()
         self._t = None
         try:
@@ -66,6 +66,10 @@ class ClockSampler:
             self.nv = pynvml
             self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
             self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            try:
+                self.power_limit_w = pynvml.nvmlDeviceGetEnforcedPowerLimit(self.h) / 1000.0
+            except Exception:
+                pass
         except Exception:
             self.nv = None
 
@@ -80,6 +84,10 @@ class ClockSampler:
         while not self._stop.is_set():
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    self.power_w.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+                except Exception:
+                    pass
                 try:
                     r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 except Exception:
@@ -104,8 +112,9 @@ class ClockSampler:
 
     def summary(self):
         s = sorted(self.samples)
+        p = sorted(self.power_w)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "power_w": p[len(p) // 2] if p else None, "power_limit_w": self.power_limit_w}
 
 
 # ----------------------------------------------------------------------------------------------- CPU baseline / reference arm

@@ -140,7 +140,7 @@ DEVI H8 layer_norm8_pre(const H8& x, bool active, int C, const int4& wq, const i
 // (last written by this same kernel one step earlier) — is fetched BEFORE griddepcontrol.wait, so under programmatic dependent
 // launch only the x row load and two one-barrier reductions remain on the critical path.
 template <int NMIX>
-__global__ void __launch_bounds__(512) ln_shift_mix_kernel(int T, int C, __half* __restrict__ x,
+__global__ void __launch_bounds__(512, 2) ln_shift_mix_kernel(int T, int C, __half* __restrict__ x,
                                                             const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
                                                             __half* __restrict__ shift, long shift_stride,
                                                             const int* __restrict__ slot_idx, MixPtrs<NMIX> mp,
@@ -155,14 +155,13 @@ __global__ void __launch_bounds__(512) ln_shift_mix_kernel(int T, int C, __half*
     __half* srow = shift + (size_t)(slot_idx ? slot_idx[b] : b) * shift_stride;
     // kept packed (8 fp16 per int4) until used: 9 x 4 registers instead of 9 x 8
     const int4 z4 = make_int4(0, 0, 0, 0);
-    int4 ww = z4, bb = z4, mx[NMIX], prevq = z4;
-#pragma unroll
-    for (int n = 0; n < NMIX; n++) mx[n] = z4;
+    // 64 registers per thread: two CTAs per SM, so the 256 rows of a decode step are ONE wave (and a CTA fits beside a GEMM CTA
+    // of the previous kernel under programmatic dependent launch).  The lerp coefficients are therefore fetched where they are
+    // used (L1/L2-resident: every CTA reads the same 6 x 8 KiB), not held across the LayerNorm.
+    int4 ww = z4, bb = z4, prevq = z4;
     if (active) {
         ww = *reinterpret_cast<const int4*>(ln_w + c0);
         bb = *reinterpret_cast<const int4*>(ln_b + c0);
-#pragma unroll
-        for (int n = 0; n < NMIX; n++) mx[n] = *reinterpret_cast<const int4*>(mp.mix[n] + c0);
         if (t == 0) prevq = *reinterpret_cast<const int4*>(srow + c0);
     }
     pdl_wait();
@@ -180,17 +179,17 @@ __global__ void __launch_bounds__(512) ln_shift_mix_kernel(int T, int C, __half*
 #pragma unroll
         for (int e = 0; e < 8; e++) acc[e] = 0.f;
 #pragma unroll 1
-        for (int z0 = 0; z0 < n_part; z0 += 4) {
-            float4 lo[4], hi[4];
+        for (int z0 = 0; z0 < n_part; z0 += 2) {
+            float4 lo[2], hi[2];
 #pragma unroll
-            for (int j = 0; j < 4; j++)
+            for (int j = 0; j < 2; j++)
                 if (z0 + j < n_part) {
                     const float4* q = reinterpret_cast<const float4*>(pr + (size_t)(z0 + j) * part_stride);
                     lo[j] = __ldcg(q);
                     hi[j] = __ldcg(q + 1);
                 }
 #pragma unroll
-            for (int j = 0; j < 4; j++)
+            for (int j = 0; j < 2; j++)
                 if (z0 + j < n_part) {
                     acc[0] += lo[j].x; acc[1] += lo[j].y; acc[2] += lo[j].z; acc[3] += lo[j].w;
                     acc[4] += hi[j].x; acc[5] += hi[j].y; acc[6] += hi[j].z; acc[7] += hi[j].w;
@@ -220,7 +219,7 @@ __global__ void __launch_bounds__(512) ln_shift_mix_kernel(int T, int C, __half*
     for (int e = 0; e < 8; e++) dx.f[e] = hr(prev.f[e] - cur.f[e]);
 #pragma unroll
     for (int n = 0; n < NMIX; n++) {
-        const H8 mv = cvt8(mx[n]);
+        const H8 mv = cvt8(__ldg(reinterpret_cast<const int4*>(mp.mix[n] + c0)));
         H8 o;
 #pragma unroll
         for (int e = 0; e < 8; e++) o.f[e] = hr(cur.f[e] + hr(dx.f[e] * mv.f[e]));
