@@ -206,7 +206,7 @@ class RWKV_x070:
         g = torch.cuda.CUDAGraph()
         side.wait_stream(cur)
         with torch.cuda.stream(side):
-            g.capture_begin()
+            g.capture_begin(capture_error_mode="thread_local")   # other workers' threads keep using CUDA during this capture
             try:
                 launch()
             finally:

@@ -21,6 +21,65 @@ class Sink:
         self.n += 1
 
 
+class CountSink:
+    def __init__(self):
+        import threading
+        self.n, self.done, self.lock = 0, 0, threading.Lock()
+
+    def put_nowait(self, x):
+        with self.lock:
+            if x[0] == "token":
+                self.n += 1
+            else:
+                self.done += 1
+
+
+def multi(a, geom):
+    """SURVEY §8(d) config 3 across GPUs: one Worker thread per GPU in ONE process, one shared task queue, no collective."""
+    import threading
+    tq = queue.Queue()
+    workers, threads = [], []
+    for k in range(a.workers):
+        dev = torch.device("cuda", k)
+        with torch.cuda.device(dev):
+            m = RWKV_x070(make_args(), state_dict=make_checkpoint(geom, seed=0, recipe="trained_like", device=dev, dtype=torch.float16),
+                          device=dev)
+        w = Worker(f"w{k}", [k], ModelLoadConfig(vocab_size=geom.vocab_size), tq, batch_size=a.slots, model=m)
+        w.max_prefill_count = a.slots
+        w.pipeline = not a.no_pipeline
+        workers.append(w)
+    g = torch.Generator().manual_seed(0)
+    sink = CountSink()
+    kw = {} if a.sampled else dict(top_k=1, presence_penalty=0.0, frequency_penalty=0.0)
+    total = a.requests * a.workers
+    tasks = []
+    for i in range(total):
+        n = int(torch.randint(16, 65, (1,), generator=g))
+        tasks.append(Task(prefill_tokens=torch.randint(1, geom.vocab_size, (n,), generator=g).tolist(), output_queue=sink,
+                          max_tokens=a.max_tokens, stop_tokens=[], **kw))
+    for w in workers:
+        th = threading.Thread(target=w.start, daemon=True, name=w.worker_id)
+        threads.append(th)
+        th.start()
+    time.sleep(2.0)                       # workers initialised and idle
+    t0 = time.perf_counter()
+    for t in tasks:
+        tq.put(t)
+    while sink.done < total:
+        time.sleep(0.002)
+    dt = time.perf_counter() - t0
+    for w in workers:
+        w._stop = True
+    for th in threads:
+        th.join(timeout=10)
+    per = [w.steps["decode_tokens"] for w in workers]
+    print(json.dumps({"config": f"{a.geom} worker loop x{a.workers} GPUs (threads of one process, one task queue), {a.slots} slots each, "
+                                f"{total} requests x {a.max_tokens} new tokens, "
+                                + ("sampled (T 1.0, top_p 0.3, penalties 0.5)" if a.sampled else "greedy, penalties 0"),
+                      "decode_tok_per_s_whole_job_aggregate": sum(per) / dt, "wall_s": dt, "decode_tokens_per_worker": per,
+                      "decode_steps_per_worker": [w.steps["decode"] for w in workers], "tokens_delivered": sink.n}))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--geom", default="7.2B"); ap.add_argument("--slots", type=int, default=256)
@@ -28,8 +87,12 @@ def main():
     ap.add_argument("--sampled", action="store_true", help="temperature 1.0, top_p 0.3, penalties 0.5 (the reference's defaults)")
     ap.add_argument("--profile", action="store_true", help="host-side wall time of the pieces of a step (no device sync added)")
     ap.add_argument("--no-pipeline", action="store_true")
+    ap.add_argument("--workers", type=int, default=1, help="> 1: that many Worker threads, one per GPU, pulling from ONE task queue "
+                    "(chirrup/engine_core.py:71, :135-153); --requests is per worker")
     a = ap.parse_args()
     geom = GEOMETRIES[a.geom]
+    if a.workers > 1:
+        return multi(a, geom)
     dev = torch.device("cuda")
     m = RWKV_x070(make_args(), state_dict=make_checkpoint(geom, seed=0, recipe="trained_like", device=dev, dtype=torch.float16))
     w = Worker("w0", [0], ModelLoadConfig(vocab_size=geom.vocab_size), queue.Queue(), batch_size=a.slots, model=m)   # no scratch row: slots are addressed by index, never swapped
