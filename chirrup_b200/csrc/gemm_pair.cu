@@ -386,6 +386,177 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------------
+// Prefill-sized token counts (M > 256: several 256-row M blocks).  Same CTA-pair tile, but PERSISTENT: one pair per SM pair
+// walks a list of (M block, N tile) tiles, the fp32 accumulator is double-buffered in TMEM (2 x 256 columns), so the four
+// epilogue warps drain tile i while the MMA thread already accumulates tile i+1 and the TMA ring never drains between tiles.
+// Tile order: groups of PERSIST_GM consecutive M blocks, N-tile-major inside a group — the pairs of one wave share a few W
+// tiles and the group's activation rows stay in L2, so the weights stream from HBM once per group.
+constexpr int PERSIST_STAGES = 5;
+constexpr int PERSIST_GM = 8;
+constexpr uint32_t PERSIST_TMEM_COLS = 512;
+constexpr int PERSIST_SMEM_BYTES = PERSIST_STAGES * PAIR_STAGE_BYTES + PAIR_STAGING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+struct TileCoord {
+    int pi, m0, n0, local_tile;
+};
+DEVI TileCoord persist_tile(const PairGroup& grp, int tile, int NT, int gy) {
+    const int per_group = PERSIST_GM * NT;
+    const int grp_i = tile / per_group;
+    const int r = tile - grp_i * per_group;
+    const int gm = min(PERSIST_GM, gy - grp_i * PERSIST_GM);
+    const int nt = r / gm;
+    const int mb = grp_i * PERSIST_GM + (r - nt * gm);
+    int pi = 0;
+    while (pi + 1 < grp.n && nt >= grp.p[pi].tile_end) pi++;
+    TileCoord c;
+    c.pi = pi;
+    c.local_tile = nt - (pi ? grp.p[pi - 1].tile_end : 0);
+    c.n0 = c.local_tile * grp.p[pi].bn;
+    c.m0 = mb * 256;
+    return c;
+}
+DEVI void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+
+__global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(const __grid_constant__ PairGroup grp, int gy) {
+    extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* staging = smem + PERSIST_STAGES * PAIR_STAGE_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + PAIR_STAGING_BYTES);
+    uint64_t* empty_bar = full_bar + PERSIST_STAGES;
+    uint64_t* tfull_bar = empty_bar + PERSIST_STAGES;   // [2] accumulator buffer complete (arrives in both CTAs)
+    uint64_t* tempty_bar = tfull_bar + 2;               // [2] accumulator buffer drained by all 8 epilogue warps of the pair (leader's)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t crank = cluster_ctarank();
+    const int pr = crank & 1;
+    const int pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    const int NT = grp.p[grp.n - 1].tile_end;
+    const int total = NT * gy;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < grp.n; i++) {
+            tma_prefetch_desc(&grp.p[i].tmA);
+            tma_prefetch_desc(&grp.p[i].tmW);
+        }
+        for (int s = 0; s < PERSIST_STAGES; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int b = 0; b < 2; b++) {
+            mbar_init(&tfull_bar[b], 1);
+            mbar_init(&tempty_bar[b], 8);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_slot, PERSIST_TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    cluster_arrive_wait();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            const uint64_t pol_w = policy_evict_last();   // every W tile is re-read by the other M blocks of the group
+            const uint64_t pol_a = policy_evict_last();
+            const uint32_t leader = crank & ~1u;
+            int s = 0;
+            uint32_t ph = 0;
+            for (int tile = pair_id; tile < total; tile += n_pairs) {
+                const TileCoord c = persist_tile(grp, tile, NT, gy);
+                const PairProblem& P = grp.p[c.pi];
+                const int bn = P.bn;
+                const int n_kb = (P.g.K + BK - 1) / BK;
+                const uint32_t tx = 2u * (128u * BK * 2u + (uint32_t)(bn >> 1) * BK * 2u);
+                for (int kb = 0; kb < n_kb; kb++) {
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    uint8_t* st = smem + s * PAIR_STAGE_BYTES;
+                    if (pr == 0) mbar_arrive_expect_tx(&full_bar[s], tx);
+                    const uint32_t bar = mapa_shared(smem_u32(&full_bar[s]), leader);
+                    tma_load_2d_pair(st, &P.tmA, kb * BK, c.m0 + pr * 128, bar, pol_a);
+                    tma_load_2d_pair(st + 128 * BK * 2, &P.tmW, kb * BK, c.n0 + pr * (bn >> 1), bar, pol_w);
+                    if (++s == PERSIST_STAGES) {
+                        s = 0;
+                        ph ^= 1;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (pr == 0 && lane == 0) {
+            const uint16_t mask = (uint16_t)(3u << (crank & ~1u));
+            int s = 0;
+            uint32_t ph = 0;
+            int j = 0;
+            for (int tile = pair_id; tile < total; tile += n_pairs, j++) {
+                const TileCoord c = persist_tile(grp, tile, NT, gy);
+                const PairProblem& P = grp.p[c.pi];
+                const int n_kb = (P.g.K + BK - 1) / BK;
+                const uint32_t idesc = umma_idesc_f16(256, (uint32_t)P.bn);
+                const int buf = j & 1;
+                mbar_wait(&tempty_bar[buf], (uint32_t)((j >> 1) & 1) ^ 1);  // the epilogue of tile j-2 has drained this buffer
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)buf * 256u;
+                for (int kb = 0; kb < n_kb; kb++) {
+                    mbar_wait(&full_bar[s], ph);
+                    tc_fence_after();
+                    const uint32_t st = smem_u32(smem + s * PAIR_STAGE_BYTES);
+                    const uint64_t adesc = umma_desc_sw128(st);
+                    const uint64_t bdesc = umma_desc_sw128(st + 128 * BK * 2);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; k++)
+                        umma_f16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_commit_pair(&empty_bar[s], mask);
+                    if (++s == PERSIST_STAGES) {
+                        s = 0;
+                        ph ^= 1;
+                    }
+                }
+                umma_commit_pair(&tfull_bar[buf], mask);
+            }
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3;
+        const uint32_t stg0 = smem_u32(staging) + (uint32_t)q * (2 * 32 * STG_LD * 4);
+        const uint32_t tempty_leader0 = mapa_shared(smem_u32(&tempty_bar[0]), crank & ~1u);
+        int j = 0;
+        for (int tile = pair_id; tile < total; tile += n_pairs, j++) {
+            const TileCoord c = persist_tile(grp, tile, NT, gy);
+            const PairProblem& P = grp.p[c.pi];
+            const GemmArgs& g = P.g;
+            EpiCtx ec;
+            ec.out = g.out; ec.bias = g.bias; ec.residual = g.residual; ec.ldo = g.ldo; ec.M = g.M; ec.N = g.N;
+            int n_valid = (g.N - c.n0 + 31) >> 5;
+            if (n_valid > (P.bn >> 5)) n_valid = P.bn >> 5;
+            const int buf = j & 1;
+            mbar_wait(&tfull_bar[buf], (uint32_t)(j >> 1) & 1);
+            tc_fence_after();
+            const int epi = g.epi;
+            EPI_DISPATCH(epi, epilogue_direct<E>(tmem_base + (uint32_t)buf * 256u, q, lane, n_valid, ec, c.m0 + pr * 128 + q * 32, c.n0, stg0));
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(tempty_leader0 + (uint32_t)buf * 8u);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_arrive_wait();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, PERSIST_TMEM_COLS);
+    }
+}
+
 constexpr int PAIR_SMEM_BYTES = PAIR_MAX_STAGES * PAIR_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 static_assert(PAIR_STAGING_BYTES + 8 * PAIR_UNIT_FLOATS * 4 <= PAIR_MAX_STAGES * PAIR_STAGE_BYTES, "landing zone must fit the stages");
 
@@ -414,6 +585,34 @@ int pair_slots(int s) {
         n = 148 / (2 * s) - (s > 1 ? 2 : 0);  // conservative guess
     }
     cache[dev][s] = n;
+    return n;
+}
+
+// CTA pairs of the persistent kernel the device can hold at once (one per SM pair).
+int persist_slots() {
+    static int cache[8] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 8) dev = 0;
+    if (cache[dev]) return cache[dev];
+    cudaFuncSetAttribute(pair_gemm_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PERSIST_SMEM_BYTES);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2, 1, 1);
+    cfg.blockDim = dim3(PAIR_THREADS);
+    cfg.dynamicSmemBytes = PERSIST_SMEM_BYTES;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, pair_gemm_persist_kernel, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = 72;
+    }
+    cache[dev] = n;
     return n;
 }
 
@@ -446,6 +645,61 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
             return B200_ERR_UNSUPPORTED;
         const int kb = (d[i].K + BK - 1) / BK;
         if (kb < min_kb) min_kb = kb;
+    }
+    static const bool persist_env = getenv("B200_NO_PERSIST") == nullptr;
+    if (gy >= 2 && persist_env) {  // prefill-sized M: persistent pairs, double-buffered accumulators (no K split, BN = 256)
+        PairGroup grp;
+        grp.n = n;
+        grp.n_stages = PERSIST_STAGES;
+        int end = 0;
+        for (int i = 0; i < n; i++) {
+            int bn = 256;
+            const int n32 = (d[i].N + 31) / 32 * 32;
+            if (bn > n32) bn = n32;
+            PairProblem& P = grp.p[i];
+            int rc = make_tmap_2d_f16(&P.tmA, d[i].A, (uint64_t)M, (uint64_t)d[i].K, (uint64_t)d[i].lda * 2, 128, BK,
+                                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+            if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+            rc = make_tmap_2d_f16(&P.tmW, d[i].W, (uint64_t)d[i].N, (uint64_t)d[i].K, (uint64_t)d[i].ldw * 2, bn / 2, BK,
+                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+            if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+            GemmArgs& g = P.g;
+            g.M = M; g.N = d[i].N; g.K = d[i].K;
+            g.out = static_cast<__half*>(d[i].out);
+            g.ldo = d[i].ldo;
+            g.bias = static_cast<const __half*>(d[i].bias);
+            g.residual = static_cast<const __half*>(d[i].residual);
+            g.epi = d[i].epi;
+            if (g.epi < B200_EPI_NONE || g.epi > B200_EPI_RESADD || (g.epi == B200_EPI_RESADD && !g.residual)) return B200_ERR_BAD_ARG;
+            g.partials = nullptr; g.kb_per_split = (d[i].K + BK - 1) / BK; g.n_split = 1; g.dbg = nullptr; g.defer = nullptr;
+            end += (d[i].N + bn - 1) / bn;
+            P.tile_end = end;
+            P.bn = bn;
+        }
+        for (int i = n; i < PAIR_MAX_GROUP; i++) {
+            grp.p[i].tile_end = end;
+            grp.p[i].bn = 32;
+        }
+        const long total = (long)end * gy;
+        const int slots = persist_slots();
+        const int pairs = (int)(total < slots ? total : slots);
+        cudaError_t e = cudaFuncSetAttribute(pair_gemm_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PERSIST_SMEM_BYTES);
+        if (e != cudaSuccess) return (int)e;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2 * pairs, 1, 1);
+        cfg.blockDim = dim3(PAIR_THREADS);
+        cfg.dynamicSmemBytes = PERSIST_SMEM_BYTES;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[2];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[1].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl ? 2 : 1;
+        return (int)cudaLaunchKernelEx(&cfg, pair_gemm_persist_kernel, grp, gy);
     }
     // tile widths and the common K split: minimise waves x (time of the slowest CTA)
     static const int force_bn = getenv("B200_PAIR_BN") ? atoi(getenv("B200_PAIR_BN")) : 0;  // tuning overrides
