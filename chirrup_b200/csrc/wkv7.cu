@@ -188,7 +188,7 @@ DEVI void fused_load(FusedIn& f, const WkvFusedArgs& p, size_t idx) {
     }
 }
 
-__global__ void __launch_bounds__(HS, 12) wkv7_fused_kernel(const __grid_constant__ CUtensorMap tm_state, const WkvFusedArgs p) {
+__global__ void __launch_bounds__(HS, 14) wkv7_fused_kernel(const __grid_constant__ CUtensorMap tm_state, const WkvFusedArgs p) {
     __shared__ __align__(1024) uint8_t tile[HS * HS * 2];
     __shared__ __align__(16) __half sv[5][HS];  // w~, k, a, b, r of the current token
     __shared__ float red[4][2];
