@@ -630,6 +630,62 @@ double pair_cta_cost(int bn, int s, int kps, bool defer = false) {
 
 int pair_slots_query(int s) { return (s >= 1 && s <= PAIR_MAX_SPLIT) ? pair_slots(s) : 0; }
 
+// Prefill-sized M: persistent pairs, double-buffered accumulators (no K split, BN = 256).
+static int persist_group_launch(int n, const LinearDesc* d, int M, int gy, cudaStream_t stream, bool pdl) {
+    PairGroup grp;
+    grp.n = n;
+    grp.n_stages = PERSIST_STAGES;
+    int end = 0;
+    for (int i = 0; i < n; i++) {
+        int bn = 256;
+        const int n32 = (d[i].N + 31) / 32 * 32;
+        if (bn > n32) bn = n32;
+        PairProblem& P = grp.p[i];
+        int rc = make_tmap_2d_f16(&P.tmA, d[i].A, (uint64_t)M, (uint64_t)d[i].K, (uint64_t)d[i].lda * 2, 128, BK,
+                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+        if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+        rc = make_tmap_2d_f16(&P.tmW, d[i].W, (uint64_t)d[i].N, (uint64_t)d[i].K, (uint64_t)d[i].ldw * 2, bn / 2, BK,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+        if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+        GemmArgs& g = P.g;
+        g.M = M; g.N = d[i].N; g.K = d[i].K;
+        g.out = static_cast<__half*>(d[i].out);
+        g.ldo = d[i].ldo;
+        g.bias = static_cast<const __half*>(d[i].bias);
+        g.residual = static_cast<const __half*>(d[i].residual);
+        g.epi = d[i].epi;
+        if (g.epi < B200_EPI_NONE || g.epi > B200_EPI_RESADD || (g.epi == B200_EPI_RESADD && !g.residual)) return B200_ERR_BAD_ARG;
+        g.partials = nullptr; g.kb_per_split = (d[i].K + BK - 1) / BK; g.n_split = 1; g.dbg = nullptr; g.defer = nullptr;
+        end += (d[i].N + bn - 1) / bn;
+        P.tile_end = end;
+        P.bn = bn;
+    }
+    for (int i = n; i < PAIR_MAX_GROUP; i++) {
+        grp.p[i].tile_end = end;
+        grp.p[i].bn = 32;
+    }
+    const long total = (long)end * gy;
+    const int slots = persist_slots();
+    const int pairs = (int)(total < slots ? total : slots);
+    cudaError_t e = cudaFuncSetAttribute(pair_gemm_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PERSIST_SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs, 1, 1);
+    cfg.blockDim = dim3(PAIR_THREADS);
+    cfg.dynamicSmemBytes = PERSIST_SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 2 : 1;
+    return (int)cudaLaunchKernelEx(&cfg, pair_gemm_persist_kernel, grp, gy);
+}
+
 // Up to PAIR_MAX_GROUP linear layers that share M (> 128) in ONE launch.  Returns B200_ERR_UNSUPPORTED when the group does
 // not fit this kernel (the caller then uses gemm.cu).
 int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream, bool pdl,
@@ -645,61 +701,6 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
             return B200_ERR_UNSUPPORTED;
         const int kb = (d[i].K + BK - 1) / BK;
         if (kb < min_kb) min_kb = kb;
-    }
-    static const bool persist_env = getenv("B200_NO_PERSIST") == nullptr;
-    if (gy >= 2 && persist_env) {  // prefill-sized M: persistent pairs, double-buffered accumulators (no K split, BN = 256)
-        PairGroup grp;
-        grp.n = n;
-        grp.n_stages = PERSIST_STAGES;
-        int end = 0;
-        for (int i = 0; i < n; i++) {
-            int bn = 256;
-            const int n32 = (d[i].N + 31) / 32 * 32;
-            if (bn > n32) bn = n32;
-            PairProblem& P = grp.p[i];
-            int rc = make_tmap_2d_f16(&P.tmA, d[i].A, (uint64_t)M, (uint64_t)d[i].K, (uint64_t)d[i].lda * 2, 128, BK,
-                                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
-            if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
-            rc = make_tmap_2d_f16(&P.tmW, d[i].W, (uint64_t)d[i].N, (uint64_t)d[i].K, (uint64_t)d[i].ldw * 2, bn / 2, BK,
-                                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
-            if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
-            GemmArgs& g = P.g;
-            g.M = M; g.N = d[i].N; g.K = d[i].K;
-            g.out = static_cast<__half*>(d[i].out);
-            g.ldo = d[i].ldo;
-            g.bias = static_cast<const __half*>(d[i].bias);
-            g.residual = static_cast<const __half*>(d[i].residual);
-            g.epi = d[i].epi;
-            if (g.epi < B200_EPI_NONE || g.epi > B200_EPI_RESADD || (g.epi == B200_EPI_RESADD && !g.residual)) return B200_ERR_BAD_ARG;
-            g.partials = nullptr; g.kb_per_split = (d[i].K + BK - 1) / BK; g.n_split = 1; g.dbg = nullptr; g.defer = nullptr;
-            end += (d[i].N + bn - 1) / bn;
-            P.tile_end = end;
-            P.bn = bn;
-        }
-        for (int i = n; i < PAIR_MAX_GROUP; i++) {
-            grp.p[i].tile_end = end;
-            grp.p[i].bn = 32;
-        }
-        const long total = (long)end * gy;
-        const int slots = persist_slots();
-        const int pairs = (int)(total < slots ? total : slots);
-        cudaError_t e = cudaFuncSetAttribute(pair_gemm_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PERSIST_SMEM_BYTES);
-        if (e != cudaSuccess) return (int)e;
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(2 * pairs, 1, 1);
-        cfg.blockDim = dim3(PAIR_THREADS);
-        cfg.dynamicSmemBytes = PERSIST_SMEM_BYTES;
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[2];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[1].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = pdl ? 2 : 1;
-        return (int)cudaLaunchKernelEx(&cfg, pair_gemm_persist_kernel, grp, gy);
     }
     // tile widths and the common K split: minimise waves x (time of the slowest CTA)
     static const int force_bn = getenv("B200_PAIR_BN") ? atoi(getenv("B200_PAIR_BN")) : 0;  // tuning overrides
@@ -742,6 +743,23 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
                 for (int i = 0; i < n; i++) best_bn[i] = bns[i];
             }
         }
+    }
+    // Several M blocks: the persistent kernel wins once every pair has a few tiles to walk (its accumulator double-buffering and
+    // never-draining ring pay per tile boundary); with few tiles and long K the one-tile kernel's K split is worth more.
+    static const bool persist_env = getenv("B200_NO_PERSIST") == nullptr;
+    if (gy >= 2 && persist_env) {
+        long tiles = 0;
+        double work = 0.0;  // tile x K-block iterations at BN = 256
+        for (int i = 0; i < n; i++) {
+            const long t = (long)((d[i].N + 255) / 256) * gy;
+            tiles += t;
+            work += (double)t * ((d[i].K + BK - 1) / BK);
+        }
+        const int slots = persist_slots();
+        const long pairs = tiles < slots ? tiles : slots;
+        const double rounds = (double)((tiles + pairs - 1) / pairs);
+        const double persist_cost = 5.0 + rounds * (work / tiles) * 0.40;
+        if (persist_cost < best_cost) return persist_group_launch(n, d, M, gy, stream, pdl);
     }
     // Deferred reduction (one residual-add problem, consumer sums the partials): the K split is then over independent CTA
     // pairs — no cluster along z, so S is not limited by the 15 clusters of 8 the device co-schedules (FFN value: 16 tiles x 4).
