@@ -20,7 +20,21 @@ def slot_bytes(state: List[torch.Tensor]) -> int:
 def extract_slot(state: List[torch.Tensor], slot: int, device=None, non_blocking: bool = True) -> List[torch.Tensor]:
     """Copy of one slot in the reference's single-request layout ((L,2,1,C), (L,1,H,64,64), (1,)) — what Chirrup caches
     (``chirrup/utils/state_cache.py``) and re-injects through ``Task.state``."""
-    dev = device if device is not None else state[0].device
+    dev = torch.device(device) if device is not None else state[0].device
+    if dev.type == "cuda" and state[0].is_cuda:                 # device target: strided DMA copies (b200_slot_copy)
+        s0, s1 = state[0], state[1]
+        out = [torch.empty((s0.shape[0], 2, 1, s0.shape[3]), dtype=s0.dtype, device=dev),
+               torch.empty((s1.shape[0], 1) + tuple(s1.shape[2:]), dtype=s1.dtype, device=dev),
+               state[2][slot:slot + 1].to(dev, non_blocking=non_blocking, copy=True)]
+        if dev != s0.device:
+            _enable_peer(s0.device, dev)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(s0.device))
+            torch.cuda.current_stream(dev).wait_event(ev)
+        with torch.cuda.device(dev):
+            _copy_rows(out[0][:, :, 0], s0[:, :, slot])
+            _copy_rows(out[1][:, 0], s1[:, slot])
+        return out
     out = [state[0][:, :, slot:slot + 1].to(dev, non_blocking=non_blocking, copy=True),
            state[1][:, slot:slot + 1].to(dev, non_blocking=non_blocking, copy=True),
            state[2][slot:slot + 1].to(dev, non_blocking=non_blocking, copy=True)]
@@ -30,8 +44,15 @@ def extract_slot(state: List[torch.Tensor], slot: int, device=None, non_blocking
 def inject_slot(state: List[torch.Tensor], slot: int, packed: List[torch.Tensor], non_blocking: bool = True) -> None:
     """``batch_state[i][..., slot, ...] = task.state[i]`` (``chirrup/worker.py:595-597``); source may live on another GPU or on
     the host."""
-    state[0][:, :, slot:slot + 1].copy_(packed[0].view(state[0].shape[0], 2, 1, -1), non_blocking=non_blocking)
-    state[1][:, slot:slot + 1].copy_(packed[1].view(state[1].shape[0], 1, *state[1].shape[2:]), non_blocking=non_blocking)
+    p0 = packed[0].view(state[0].shape[0], 2, 1, -1)
+    p1 = packed[1].view(state[1].shape[0], 1, *state[1].shape[2:])
+    if p0.is_cuda and state[0].is_cuda and p0.device == state[0].device and p0.dtype == state[0].dtype:
+        with torch.cuda.device(state[0].device):
+            _copy_rows(state[0][:, :, slot], p0[:, :, 0])
+            _copy_rows(state[1][:, slot], p1[:, 0])
+    else:
+        state[0][:, :, slot:slot + 1].copy_(p0, non_blocking=non_blocking)
+        state[1][:, slot:slot + 1].copy_(p1, non_blocking=non_blocking)
     state[2][slot:slot + 1].copy_(packed[2].view(1), non_blocking=non_blocking)
 
 
