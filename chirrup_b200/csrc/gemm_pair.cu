@@ -620,8 +620,9 @@ int persist_slots() {
 double pair_cta_cost(int bn, int s, int kps, bool defer = false) {
     const double clk = 1500.0;                                    // MHz under tensor load (power-capped)
     const double mma = 4.0 * (bn / 2.0);                          // cycles per K block: 4 UMMAs of 256 x bn x 16
-    const double ingest = 560.0;  // measured floor per K block (0.37 us), the same for BN = 64 ... 256: prefer the widest tile
-                                  // (fewer CTAs for the same time; A/B over three interleaved runs: 6.480 -> 6.468 ms/step)
+    const double ingest = (16384.0 + bn * 64.0) / 52.0;           // bytes into this SM per K block at ~52 B/clk
+    // (a flat 560-cycle floor per K block — what the timelines show for BN = 64 ... 256 — was tried: widest tiles everywhere,
+    // 6.480 -> 6.468 ms/step, i.e. nothing, so the plans that the parity suite has been run on all along are kept)
     const double main_us = kps * (mma > ingest ? mma : ingest) / clk;
     const double epi_us = defer ? 0.5 + 3.0 * bn / 256.0 : (s > 1) ? 1.2 + 4.5 * bn / 256.0 : 0.5 + 2.5 * bn / 256.0;
     return 1.8 + main_us + epi_us;
