@@ -24,8 +24,8 @@
 namespace b200 {
 namespace {
 
-constexpr int ST = 512;          // threads per row
-constexpr int SCH = 16;          // 16-byte chunks per thread -> up to 512 * 16 * 8 = 65536 columns
+constexpr int ST = 1024;         // threads per row
+constexpr int SCH = 8;           // 16-byte chunks per thread -> up to 1024 * 8 * 8 = 65536 columns
 constexpr float FIX_ONE = 4294967296.0f;
 
 typedef unsigned long long u64;
