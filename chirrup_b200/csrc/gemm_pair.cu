@@ -749,7 +749,9 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
     // Several M blocks: the persistent kernel wins once every pair has a few tiles to walk (its accumulator double-buffering and
     // never-draining ring pay per tile boundary); with few tiles and long K the one-tile kernel's K split is worth more.
     static const bool persist_env = getenv("B200_NO_PERSIST") == nullptr;
-    if (gy >= 2 && persist_env) {
+    long tiles256 = 0;
+    for (int i = 0; i < n; i++) tiles256 += (long)((d[i].N + 255) / 256) * gy;
+    if ((gy >= 2 || (n == 1 && tiles256 >= 3L * persist_slots())) && persist_env) {  // also one wide problem (the head: 256 tiles)
         long tiles = 0;
         double work = 0.0;  // tile x K-block iterations at BN = 256
         for (int i = 0; i < n; i++) {
