@@ -460,22 +460,44 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
     cluster_arrive_wait();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
-            const uint64_t pol_w = policy_evict_last();   // every W tile is re-read by the other M blocks of the group
+            const uint64_t pol_w = gy > 1 ? policy_evict_last() : policy_evict_first();  // W tiles are re-read only across M blocks
             const uint64_t pol_a = policy_evict_last();
             const uint32_t leader = crank & ~1u;
             int s = 0;
             uint32_t ph = 0;
+            // the first tile's first ring of weight tiles does not depend on the preceding kernel: request it before the wait
+            int npre = 0;
+            if (pair_id < total) {
+                const TileCoord c = persist_tile(grp, pair_id, NT, gy);
+                const PairProblem& P = grp.p[c.pi];
+                const int bn = P.bn;
+                const int n_kb = (P.g.K + BK - 1) / BK;
+                const uint32_t tx = 2u * (128u * BK * 2u + (uint32_t)(bn >> 1) * BK * 2u);
+                npre = min(n_kb, PERSIST_STAGES);
+                for (int kb = 0; kb < npre; kb++) {
+                    if (pr == 0) mbar_arrive_expect_tx(&full_bar[kb], tx);
+                    tma_load_2d_pair(smem + kb * PAIR_STAGE_BYTES + 128 * BK * 2, &P.tmW, kb * BK, c.n0 + pr * (bn >> 1),
+                                     mapa_shared(smem_u32(&full_bar[kb]), leader), pol_w);
+                }
+                pdl_wait();
+                for (int kb = 0; kb < npre; kb++)
+                    tma_load_2d_pair(smem + kb * PAIR_STAGE_BYTES, &P.tmA, kb * BK, c.m0 + pr * 128,
+                                     mapa_shared(smem_u32(&full_bar[kb]), leader), pol_a);
+                s = npre % PERSIST_STAGES;
+                ph = (uint32_t)(npre / PERSIST_STAGES) & 1;
+            } else {
+                pdl_wait();
+            }
             for (int tile = pair_id; tile < total; tile += n_pairs) {
                 const TileCoord c = persist_tile(grp, tile, NT, gy);
                 const PairProblem& P = grp.p[c.pi];
                 const int bn = P.bn;
                 const int n_kb = (P.g.K + BK - 1) / BK;
                 const uint32_t tx = 2u * (128u * BK * 2u + (uint32_t)(bn >> 1) * BK * 2u);
-                for (int kb = 0; kb < n_kb; kb++) {
+                for (int kb = (tile == pair_id ? npre : 0); kb < n_kb; kb++) {
                     mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t* st = smem + s * PAIR_STAGE_BYTES;
                     if (pr == 0) mbar_arrive_expect_tx(&full_bar[s], tx);
@@ -488,9 +510,12 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
                     }
                 }
             }
+        } else {
+            pdl_wait();
         }
         __syncwarp();
     } else if (warp == 1) {
+        pdl_wait();
         if (pr == 0 && lane == 0) {
             const uint16_t mask = (uint16_t)(3u << (crank & ~1u));
             int s = 0;
@@ -525,6 +550,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
         }
         __syncwarp();
     } else {
+        pdl_wait();
         const int q = warp & 3;
         const uint32_t stg0 = smem_u32(staging) + (uint32_t)q * (2 * 32 * STG_LD * 4);
         const uint32_t tempty_leader0 = mapa_shared(smem_u32(&tempty_bar[0]), crank & ~1u);
