@@ -139,6 +139,27 @@ DEVI void epilogue_direct(uint32_t tmem_base, int q, int lane, int n_valid, cons
     }
 }
 
+// The same with ONE staging buffer per warp (the persistent kernel spends its shared memory on a sixth pipeline stage): a warp
+// barrier separates the reads of unit u from the writes of unit u+1.
+template <int EPI>
+DEVI void epilogue_direct_1buf(uint32_t tmem_base, int q, int lane, int n_valid, const EpiCtx& c, int row0, int n0, uint32_t stg0) {
+    float va[32], vb[32];
+    tmem_ld_unit(tmem_base, q, 0, va);
+#pragma unroll 1
+    for (int u = 0; u < n_valid; u += 2) {
+        tmem_ld_wait();
+        if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
+        __syncwarp();
+        emit_unit<EPI>(va, stg0, c, row0, n0 + u * 32, lane);
+        if (u + 1 < n_valid) {
+            tmem_ld_wait();
+            if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
+            __syncwarp();
+            emit_unit<EPI>(vb, stg0, c, row0, n0 + (u + 1) * 32, lane);
+        }
+    }
+}
+
 // K split: sum the S landed partials of each of this CTA's units in split order, then emit.
 template <int EPI>
 DEVI void epilogue_reduce(uint32_t land, int S, int split, int n_valid, int row, int lane, const EpiCtx& c, int row0, int n0,
@@ -392,10 +413,11 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
 // epilogue warps drain tile i while the MMA thread already accumulates tile i+1 and the TMA ring never drains between tiles.
 // Tile order: groups of PERSIST_GM consecutive M blocks, N-tile-major inside a group — the pairs of one wave share a few W
 // tiles and the group's activation rows stay in L2, so the weights stream from HBM once per group.
-constexpr int PERSIST_STAGES = 5;
+constexpr int PERSIST_STAGES = 6;
+constexpr int PERSIST_STAGING_BYTES = 4 * 32 * STG_LD * 4;  // one 32 x 32(+4) fp32 buffer per epilogue warp = 18 KiB
 constexpr int PERSIST_GM = 8;
 constexpr uint32_t PERSIST_TMEM_COLS = 512;
-constexpr int PERSIST_SMEM_BYTES = PERSIST_STAGES * PAIR_STAGE_BYTES + PAIR_STAGING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int PERSIST_SMEM_BYTES = PERSIST_STAGES * PAIR_STAGE_BYTES + PERSIST_STAGING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 
 struct TileCoord {
     int pi, m0, n0, local_tile;
@@ -425,7 +447,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
     pdl_launch_dependents();
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* staging = smem + PERSIST_STAGES * PAIR_STAGE_BYTES;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + PAIR_STAGING_BYTES);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + PERSIST_STAGING_BYTES);
     uint64_t* empty_bar = full_bar + PERSIST_STAGES;
     uint64_t* tfull_bar = empty_bar + PERSIST_STAGES;   // [2] accumulator buffer complete (arrives in both CTAs)
     uint64_t* tempty_bar = tfull_bar + 2;               // [2] accumulator buffer drained by all 8 epilogue warps of the pair (leader's)
@@ -552,7 +574,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
     } else {
         pdl_wait();
         const int q = warp & 3;
-        const uint32_t stg0 = smem_u32(staging) + (uint32_t)q * (2 * 32 * STG_LD * 4);
+        const uint32_t stg0 = smem_u32(staging) + (uint32_t)q * (32 * STG_LD * 4);
         const uint32_t tempty_leader0 = mapa_shared(smem_u32(&tempty_bar[0]), crank & ~1u);
         int j = 0;
         for (int tile = pair_id; tile < total; tile += n_pairs, j++) {
@@ -567,7 +589,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
             mbar_wait(&tfull_bar[buf], (uint32_t)(j >> 1) & 1);
             tc_fence_after();
             const int epi = g.epi;
-            EPI_DISPATCH(epi, epilogue_direct<E>(tmem_base + (uint32_t)buf * 256u, q, lane, n_valid, ec, c.m0 + pr * 128 + q * 32, c.n0, stg0));
+            EPI_DISPATCH(epi, epilogue_direct_1buf<E>(tmem_base + (uint32_t)buf * 256u, q, lane, n_valid, ec, c.m0 + pr * 128 + q * 32, c.n0, stg0));
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(tempty_leader0 + (uint32_t)buf * 8u);
