@@ -46,12 +46,19 @@ struct PairProblem {
     GemmArgs g;
     int tile_end;     // one past this problem's last tile index along blockIdx.x / 2
     int bn;           // tile width: multiple of 32, <= 256
+    // persistent kernel only — chained problems inside one launch (FFN key -> FFN value):
+    int kb0;          // first K block of this problem's K range (its length is g.kb_per_split)
+    int dep_flag;     // >= 0: tiles of this problem may load A only once flags[dep_flag] >= dep_need
+    int dep_need;
+    int sig_flag;     // >= 0: every epilogue warp adds 1 to flags[sig_flag + local_tile / sig_div] when its rows are stored
+    int sig_div;
 };
 
 struct alignas(64) PairGroup {
     PairProblem p[PAIR_MAX_GROUP];
     int n;
     int n_stages;
+    int* flags;       // chained launches: [0, 8) arrival counters, [8, 16) consumer counters (both back to 0 when the launch ends)
 };
 
 DEVI uint32_t cluster_ctarank() {
@@ -156,6 +163,26 @@ DEVI void epilogue_direct_1buf(uint32_t tmem_base, int q, int lane, int n_valid,
             if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
             __syncwarp();
             emit_unit<EPI>(vb, stg0, c, row0, n0 + (u + 1) * 32, lane);
+        }
+    }
+}
+
+// Raw fp32 tile (deferred K-split partial, see GemmArgs::defer), one staging buffer per warp.
+DEVI void epilogue_f32_1buf(uint32_t tmem_base, int q, int lane, int n_valid, float* dst, int M, int N, int row0, int n0,
+                            uint32_t stg0) {
+    float va[32], vb[32];
+    tmem_ld_unit(tmem_base, q, 0, va);
+#pragma unroll 1
+    for (int u = 0; u < n_valid; u += 2) {
+        tmem_ld_wait();
+        if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
+        __syncwarp();
+        emit_unit_f32(va, stg0, dst, N, M, N, row0, n0 + u * 32, lane);
+        if (u + 1 < n_valid) {
+            tmem_ld_wait();
+            if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
+            __syncwarp();
+            emit_unit_f32(vb, stg0, dst, N, M, N, row0, n0 + (u + 1) * 32, lane);
         }
     }
 }
@@ -438,6 +465,21 @@ DEVI TileCoord persist_tile(const PairGroup& grp, int tile, int NT, int gy) {
     c.m0 = mb * 256;
     return c;
 }
+// Producer side of a chained tile: wait until the tiles this one reads from have been stored by their epilogue warps
+// (generic-proxy stores, released by a fence + atomic), then order the TMA (async-proxy) reads behind that.  The last of the
+// `n_consumers` waiters puts both counters back to zero for the next launch.
+DEVI void chain_wait(int* flags, int dep_flag, int dep_need, int n_consumers) {
+    volatile int* f = flags + dep_flag;
+    while (*f < dep_need) __nanosleep(40);
+    __threadfence();
+    asm volatile("fence.proxy.async;" ::: "memory");
+    const int old = atomicAdd(flags + 8 + dep_flag, 1);
+    if (old == n_consumers - 1) {
+        flags[8 + dep_flag] = 0;
+        flags[dep_flag] = 0;
+        __threadfence();
+    }
+}
 DEVI void mbar_arrive_cluster(uint32_t cluster_addr) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
@@ -496,17 +538,18 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
                 const TileCoord c = persist_tile(grp, pair_id, NT, gy);
                 const PairProblem& P = grp.p[c.pi];
                 const int bn = P.bn;
-                const int n_kb = (P.g.K + BK - 1) / BK;
+                const int n_kb = P.g.kb_per_split;
                 const uint32_t tx = 2u * (128u * BK * 2u + (uint32_t)(bn >> 1) * BK * 2u);
                 npre = min(n_kb, PERSIST_STAGES);
                 for (int kb = 0; kb < npre; kb++) {
                     if (pr == 0) mbar_arrive_expect_tx(&full_bar[kb], tx);
-                    tma_load_2d_pair(smem + kb * PAIR_STAGE_BYTES + 128 * BK * 2, &P.tmW, kb * BK, c.n0 + pr * (bn >> 1),
+                    tma_load_2d_pair(smem + kb * PAIR_STAGE_BYTES + 128 * BK * 2, &P.tmW, (P.kb0 + kb) * BK, c.n0 + pr * (bn >> 1),
                                      mapa_shared(smem_u32(&full_bar[kb]), leader), pol_w);
                 }
                 pdl_wait();
+                if (P.dep_flag >= 0) chain_wait(grp.flags, P.dep_flag, P.dep_need, 2 * (P.tile_end - (c.pi ? grp.p[c.pi - 1].tile_end : 0)));
                 for (int kb = 0; kb < npre; kb++)
-                    tma_load_2d_pair(smem + kb * PAIR_STAGE_BYTES, &P.tmA, kb * BK, c.m0 + pr * 128,
+                    tma_load_2d_pair(smem + kb * PAIR_STAGE_BYTES, &P.tmA, (P.kb0 + kb) * BK, c.m0 + pr * 128,
                                      mapa_shared(smem_u32(&full_bar[kb]), leader), pol_a);
                 s = npre % PERSIST_STAGES;
                 ph = (uint32_t)(npre / PERSIST_STAGES) & 1;
@@ -517,15 +560,17 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
                 const TileCoord c = persist_tile(grp, tile, NT, gy);
                 const PairProblem& P = grp.p[c.pi];
                 const int bn = P.bn;
-                const int n_kb = (P.g.K + BK - 1) / BK;
+                const int n_kb = P.g.kb_per_split;
                 const uint32_t tx = 2u * (128u * BK * 2u + (uint32_t)(bn >> 1) * BK * 2u);
                 for (int kb = (tile == pair_id ? npre : 0); kb < n_kb; kb++) {
                     mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t* st = smem + s * PAIR_STAGE_BYTES;
                     if (pr == 0) mbar_arrive_expect_tx(&full_bar[s], tx);
                     const uint32_t bar = mapa_shared(smem_u32(&full_bar[s]), leader);
-                    tma_load_2d_pair(st, &P.tmA, kb * BK, c.m0 + pr * 128, bar, pol_a);
-                    tma_load_2d_pair(st + 128 * BK * 2, &P.tmW, kb * BK, c.n0 + pr * (bn >> 1), bar, pol_w);
+                    tma_load_2d_pair(st + 128 * BK * 2, &P.tmW, (P.kb0 + kb) * BK, c.n0 + pr * (bn >> 1), bar, pol_w);
+                    if (kb == 0 && P.dep_flag >= 0)  // the weights above are already on their way
+                        chain_wait(grp.flags, P.dep_flag, P.dep_need, 2 * (P.tile_end - (c.pi ? grp.p[c.pi - 1].tile_end : 0)));
+                    tma_load_2d_pair(st, &P.tmA, (P.kb0 + kb) * BK, c.m0 + pr * 128, bar, pol_a);
                     if (++s == PERSIST_STAGES) {
                         s = 0;
                         ph ^= 1;
@@ -546,7 +591,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
             for (int tile = pair_id; tile < total; tile += n_pairs, j++) {
                 const TileCoord c = persist_tile(grp, tile, NT, gy);
                 const PairProblem& P = grp.p[c.pi];
-                const int n_kb = (P.g.K + BK - 1) / BK;
+                const int n_kb = P.g.kb_per_split;
                 const uint32_t idesc = umma_idesc_f16(256, (uint32_t)P.bn);
                 const int buf = j & 1;
                 mbar_wait(&tempty_bar[buf], (uint32_t)((j >> 1) & 1) ^ 1);  // the epilogue of tile j-2 has drained this buffer
@@ -589,10 +634,19 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
             mbar_wait(&tfull_bar[buf], (uint32_t)(j >> 1) & 1);
             tc_fence_after();
             const int epi = g.epi;
-            EPI_DISPATCH(epi, epilogue_direct_1buf<E>(tmem_base + (uint32_t)buf * 256u, q, lane, n_valid, ec, c.m0 + pr * 128 + q * 32, c.n0, stg0));
+            if (g.defer) {
+                epilogue_f32_1buf(tmem_base + (uint32_t)buf * 256u, q, lane, n_valid, g.defer, g.M, g.N, c.m0 + pr * 128 + q * 32, c.n0, stg0);
+            } else {
+                EPI_DISPATCH(epi, epilogue_direct_1buf<E>(tmem_base + (uint32_t)buf * 256u, q, lane, n_valid, ec, c.m0 + pr * 128 + q * 32, c.n0, stg0));
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(tempty_leader0 + (uint32_t)buf * 8u);
+            if (P.sig_flag >= 0) {  // chained launch: this warp's rows of the tile are stored
+                __threadfence();
+                __syncwarp();
+                if (lane == 0) atomicAdd(grp.flags + P.sig_flag + c.local_tile / P.sig_div, 1);
+            }
         }
     }
 
@@ -709,7 +763,9 @@ static int persist_group_launch(int n, const LinearDesc* d, int M, int gy, cudaS
         end += (d[i].N + bn - 1) / bn;
         P.tile_end = end;
         P.bn = bn;
+        P.kb0 = 0; P.dep_flag = -1; P.dep_need = 0; P.sig_flag = -1; P.sig_div = 1;
     }
+    grp.flags = nullptr;
     for (int i = n; i < PAIR_MAX_GROUP; i++) {
         grp.p[i].tile_end = end;
         grp.p[i].bn = 32;
@@ -734,6 +790,87 @@ static int persist_group_launch(int n, const LinearDesc* d, int M, int gy, cudaS
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 2 : 1;
     return (int)cudaLaunchKernelEx(&cfg, pair_gemm_persist_kernel, grp, gy);
+}
+
+// FFN of one decode step in ONE persistent launch (Albatross/rwkv7.py:678-679): the key GEMM (relu^2, -> hidden) and the value
+// GEMM, whose K is split S ways over independent tiles that leave raw fp32 partials for the consumer (glue.h: deferred
+// reduction).  A value tile of split z starts its activation loads once the F/S hidden columns it reads have been stored
+// (flags[z]); its weights are requested before that.  Pairs that hold no key tile take value tiles first and simply wait.
+// Same tiles, same K ranges, same summation order as the two separate launches: bit-identical results.
+int ffn_chain_launch(int M, int C, int F, const void* kx, const void* Wk, void* hidden, const void* Wv, float* partials,
+                     long partials_bytes, int* flags, int* n_split, cudaStream_t stream, bool pdl) {
+    *n_split = 0;
+    const int S = 4;
+    if (M <= 128 || M > 256 || !flags || !partials) return B200_ERR_UNSUPPORTED;
+    if ((F % (S * 256)) || (C & 7) || F / S / BK < 2 || (long)S * M * C * 4 > partials_bytes) return B200_ERR_UNSUPPORTED;
+    // Opt-in (read per call): measured 0.22 ms/step SLOWER than the two launches (6.63 vs 6.41 ms) although it saves a launch
+    // boundary per layer — the persistent kernel's 254 registers keep the next kernel's CTAs off the SMs until it exits, and a
+    // 168-register build spills.  Kept, with its bit-exactness test, as the starting point for fusing the step further.
+    if (getenv("B200_CHAIN") == nullptr) return B200_ERR_UNSUPPORTED;
+    PairGroup grp;
+    grp.n = 1 + S;
+    grp.n_stages = PERSIST_STAGES;
+    grp.flags = flags;
+    int end = 0;
+    for (int i = 0; i < 1 + S; i++) {
+        PairProblem& P = grp.p[i];
+        GemmArgs& g = P.g;
+        const bool key = i == 0;
+        const int N = key ? F : C, K = key ? C : F;
+        int bn = 256;
+        const int n32 = (N + 31) / 32 * 32;
+        if (bn > n32) bn = n32;
+        int rc = make_tmap_2d_f16(&P.tmA, key ? kx : hidden, (uint64_t)M, (uint64_t)K, (uint64_t)K * 2, 128, BK,
+                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+        if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+        rc = make_tmap_2d_f16(&P.tmW, key ? Wk : Wv, (uint64_t)N, (uint64_t)K, (uint64_t)K * 2, bn / 2, BK,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+        if (rc) return rc == -1 ? B200_ERR_NO_DRIVER : rc;
+        g.M = M; g.N = N; g.K = K;
+        g.out = key ? static_cast<__half*>(hidden) : nullptr;
+        g.ldo = N;
+        g.bias = nullptr; g.residual = nullptr;
+        g.epi = key ? B200_EPI_RELU_SQ : B200_EPI_NONE;
+        g.partials = nullptr; g.n_split = 1; g.dbg = nullptr;
+        g.kb_per_split = key ? (C + BK - 1) / BK : F / S / BK;
+        g.defer = key ? nullptr : partials + (size_t)(i - 1) * M * C;
+        end += (N + bn - 1) / bn;
+        P.tile_end = end;
+        P.bn = bn;
+        P.kb0 = key ? 0 : (i - 1) * (F / S / BK);
+        P.dep_flag = key ? -1 : i - 1;
+        P.dep_need = key ? 0 : (F / S / 256) * 8;   // every key tile of the split's hidden columns, 8 epilogue warps each
+        P.sig_flag = key ? 0 : -1;
+        P.sig_div = key ? F / S / 256 : 1;
+    }
+    for (int i = 1 + S; i < PAIR_MAX_GROUP; i++) {
+        grp.p[i].tile_end = end;
+        grp.p[i].bn = 32;
+        grp.p[i].kb0 = 0; grp.p[i].dep_flag = -1; grp.p[i].dep_need = 0; grp.p[i].sig_flag = -1; grp.p[i].sig_div = 1;
+    }
+    const int slots = persist_slots();
+    // every pair must be resident at once (value tiles wait on key tiles of other pairs), and the pairs beyond the key tiles
+    // must not be needed for key tiles: one launch of at most `slots` pairs, each walking its tile list in order
+    const int pairs = end < slots ? end : slots;
+    cudaError_t e = cudaFuncSetAttribute(pair_gemm_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PERSIST_SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs, 1, 1);
+    cfg.blockDim = dim3(PAIR_THREADS);
+    cfg.dynamicSmemBytes = PERSIST_SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 2 : 1;
+    const int rc = (int)cudaLaunchKernelEx(&cfg, pair_gemm_persist_kernel, grp, 1);
+    if (rc == 0) *n_split = S;
+    return rc;
 }
 
 // Up to PAIR_MAX_GROUP linear layers that share M (> 128) in ONE launch.  Returns B200_ERR_UNSUPPORTED when the group does
@@ -799,6 +936,8 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
     static const bool persist_env = getenv("B200_NO_PERSIST") == nullptr;
     long tiles256 = 0;
     for (int i = 0; i < n; i++) tiles256 += (long)((d[i].N + 255) / 256) * gy;
+    static const bool persist_all = getenv("B200_PERSIST_ALL") != nullptr;  // experiment
+    if (persist_all && persist_env && !defer_splits) return persist_group_launch(n, d, M, gy, stream, pdl);
     if ((gy >= 2 || (n == 1 && tiles256 >= 3L * persist_slots())) && persist_env) {  // also one wide problem (the head: 256 tiles)
         long tiles = 0;
         double work = 0.0;  // tile x K-block iterations at BN = 256

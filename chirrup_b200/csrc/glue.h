@@ -87,4 +87,10 @@ int linear_group_launch(int n, const LinearDesc* d, int M, void* workspace, long
 int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long workspace_bytes, cudaStream_t stream, bool pdl,
                       unsigned long long* dbg = nullptr, int* defer_splits = nullptr);
 
+// gemm_pair.cu: FFN key + FFN value of a decode step (128 < M <= 256) in one persistent launch; the value product is left as
+// *n_split fp32 partials (layout of linear_f16_launch's deferred reduction) for the next ln_shift_mix.  `flags`: 16 ints, zero
+// before the first call (the kernel leaves them zero).  B200_ERR_UNSUPPORTED when the shapes do not fit: use two launches.
+int ffn_chain_launch(int M, int C, int F, const void* kx, const void* Wk, void* hidden, const void* Wv, float* partials,
+                     long partials_bytes, int* flags, int* n_split, cudaStream_t stream, bool pdl);
+
 }  // namespace b200

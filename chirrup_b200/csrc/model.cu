@@ -23,6 +23,7 @@ inline long align_up(long x, long a) { return (x + a - 1) / a * a; }
 
 // Workspace carve-up for M tokens.
 struct Ws {
+    int* flags;                  // 16 ints for chained launches (gemm_pair.cu), zero between launches
     int* counters_and_partials;  // linear workspace
     long lin_bytes;
     __half *x, *mix[6], *r, *k, *v, *w, *a, *g, *vg, *k2, *v2, *an, *bn, *y, *yg, *vfirst, *kx, *lora[4], *hidden, *xo;
@@ -38,6 +39,7 @@ Ws carve(const b200_model* m, long M, void* base) {
         off += align_up(bytes, 256);
         return q;
     };
+    ws.flags = reinterpret_cast<int*>(take(256));  // first, so that its place does not depend on M (chained launches keep it zero)
     ws.lin_bytes = b200_linear_workspace_bytes((int)M, m->V);
     ws.counters_and_partials = reinterpret_cast<int*>(take(ws.lin_bytes));
     const long mc = M * m->C * 2;
@@ -222,10 +224,24 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
         RUN_T(32, launch_ln_shift_mix1(B, T, C, ws.x, w[B200_LW_LN2_W], w[B200_LW_LN2_B], s0 + l * s0_layer_stride + s0_which_stride, C,
                                  slot_idx, mc, st, pdl, def_o ? partials : nullptr, def_o));
         def_o = 0;
-        RUN_T(64, lin(M, F, C, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, nullptr, nullptr, B200_EPI_RELU_SQ));
-        // the last layer's x goes to ln_out, which takes finished rows
-        RUN_T(128, lin(M, C, F, ws.hidden, w[B200_LW_FFN_VALUE], ws.x, nullptr, ws.x, B200_EPI_RESADD,
-                      (may_defer && l + 1 < L) ? &def_f : nullptr));
+        bool chained = false;
+        if (may_defer && l + 1 < L && M > 128 && M <= 256 && !no_group && !skip) {
+            // FFN key + FFN value in one persistent launch (value partials deferred to the next layer's ln_shift_mix)
+            rc = ffn_chain_launch((int)M, C, F, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, w[B200_LW_FFN_VALUE],
+                                  reinterpret_cast<float*>(ws.counters_and_partials), ws.lin_bytes, ws.flags, &def_f, st, pdl);
+            if (rc == 0) {
+                chained = true;
+                n++;
+                if (debug_sync) rc = (int)cudaStreamSynchronize(st);
+            }
+            if (rc != 0 && rc != B200_ERR_UNSUPPORTED) return rc;
+        }
+        if (!chained) {
+            RUN_T(64, lin(M, F, C, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, nullptr, nullptr, B200_EPI_RELU_SQ));
+            // the last layer's x goes to ln_out, which takes finished rows
+            RUN_T(128, lin(M, C, F, ws.hidden, w[B200_LW_FFN_VALUE], ws.x, nullptr, ws.x, B200_EPI_RESADD,
+                          (may_defer && l + 1 < L) ? &def_f : nullptr));
+        }
     }
     if (logits) {
         if (full_output) {

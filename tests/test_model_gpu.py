@@ -379,3 +379,38 @@ def test_headline_configuration_properties_7p2B_bsz256():
     assert len(m._graphs) >= 1
     assert torch.equal(lgr, la) and torch.equal(sg[1], sa[1]) and torch.equal(eg, ea)                 # (4)
     assert torch.isfinite(la.float()).all()
+
+
+def test_chained_ffn_launch_is_bit_identical_to_two_launches():
+    """Decode at the headline geometry (7.2B shapes, 3 layers, 256 rows): FFN key + FFN value in one persistent launch with
+    in-kernel dependency flags (csrc/gemm_pair.cu ffn_chain_launch) — opt-in with B200_CHAIN=1, see the note there — vs the two separate launches: same tiles,
+    same K ranges, same summation order -> every bit of the logits and of the state is equal, step after step (the flags must
+    also come back to zero every launch, or the second step would read stale hidden activations)."""
+    geom, raw, m = build("7.2B", seed=5, recipe="trained_like", n_layer=3, device="cuda")
+    del raw
+    B = 256
+    g = torch.Generator().manual_seed(4)
+    toks = torch.randint(1, geom.vocab_size, (B, 2), generator=g).tolist()
+    outs = {}
+    for mode in ("chain", "two"):
+        if mode == "chain":
+            os.environ["B200_CHAIN"] = "1"
+        else:
+            os.environ.pop("B200_CHAIN", None)
+        try:
+            st = m.generate_zero_state(B)
+            lg = m.forward_seq_batch_seperate(toks, st)
+            hist = []
+            for _ in range(5):
+                nxt = lg.float().argmax(-1)
+                lg = m.forward_seq_batch_seperate([[int(t)] for t in nxt], st)
+                hist.append(lg.clone())
+            torch.cuda.synchronize()
+            outs[mode] = (hist, st)
+        finally:
+            os.environ.pop("B200_CHAIN", None)
+    (ha, sa), (hb, sb) = outs["chain"], outs["two"]
+    for a, b in zip(ha, hb):
+        assert torch.equal(a, b)
+    assert torch.equal(sa[0], sb[0]) and torch.equal(sa[1], sb[1]) and torch.equal(sa[2], sb[2])
+    assert torch.isfinite(ha[-1].float()).all()
