@@ -79,3 +79,59 @@ def update_penalty(occurrence: torch.Tensor, alpha_presence: torch.Tensor, prese
     w = torch.tensor([0.0 if tok in no_penalty_token_ids else 1.0 for tok in tokens], dtype=torch.float32)
     occurrence[s, t] += w                                          # :541
     alpha_presence[s, t] = presence_penalty[s, 0]                  # :546-547
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+# The sampler the worker ACTUALLY imports: ``from chirrup.utils.samplers import sample_logits_rwkv_pip_compatible as
+# sample_logits_real_batch`` (chirrup/worker.py:12) — chirrup/utils/samplers.py:171-255.  Different semantics from the
+# single-sort sampler above: softmax WITHOUT temperature, top-p by cutoff VALUE (every token whose probability is >= the
+# probability at the first sorted position where the cumulative sum reaches top_p stays: ties at the cutoff are all kept),
+# top-k on the sort rank, temperature applied AFTER the filters as probs ** (1/T), multinomial.
+def _pip_filtered(logits, temperature, top_p, top_k):
+    bsz, vocab_size = logits.shape
+    zero_temp_mask = temperature == 0                                              # :193
+    temperature = torch.where(zero_temp_mask, torch.ones_like(temperature), temperature)   # :194
+    top_p = torch.where(zero_temp_mask, torch.zeros_like(top_p), top_p)            # :195
+    probs = F.softmax(logits.float(), dim=-1)                                      # :198
+    sorted_probs, sorted_indices = torch.sort(probs, descending=True, dim=-1)      # :201
+    cumulative_probs = torch.cumsum(sorted_probs, dim=-1)                          # :204
+    cutoff_positions = torch.searchsorted(cumulative_probs, top_p)                 # :209
+    cutoff_positions = torch.clamp(cutoff_positions, max=vocab_size - 1)           # :210
+    cutoff_values = torch.gather(sorted_probs, dim=1, index=cutoff_positions)      # :213
+    probs = torch.where(probs < cutoff_values, torch.zeros_like(probs), probs)     # :216
+    top_k_long = top_k.long()                                                      # :219
+    active_top_k = top_k_long > 0                                                  # :220
+    if active_top_k.any():                                                         # :222
+        effective_k = torch.where(active_top_k, top_k_long, torch.full_like(top_k_long, vocab_size))   # :225-227
+        ranks = torch.arange(vocab_size, device=logits.device).expand(bsz, vocab_size)                 # :229
+        outside_topk_sorted = ranks >= effective_k                                 # :231
+        outside_topk = torch.zeros_like(probs, dtype=torch.bool).scatter_(dim=1, index=sorted_indices, src=outside_topk_sorted)  # :234-236
+        probs.masked_fill_(outside_topk, 0.0)                                      # :238
+    need_temp = temperature != 1.0                                                 # :241
+    if need_temp.any():                                                            # :242
+        inv_temp = 1.0 / temperature                                               # :244
+        adjusted_probs = probs ** inv_temp                                         # :247
+        probs = torch.where(need_temp.expand_as(probs), adjusted_probs, probs)     # :248
+    return probs
+
+
+def sample_logits_rwkv_pip_compatible(logits: torch.Tensor, temperature: torch.Tensor, top_p: torch.Tensor,
+                                      top_k: torch.Tensor) -> torch.Tensor:
+    """samplers.py:171-255; temperature / top_p (B,1) in the worker's dtypes (fp16, worker.py:611-620), top_k (B,1) int32."""
+    return torch.multinomial(_pip_filtered(logits, temperature, top_p, top_k), num_samples=1).squeeze(-1)    # :253
+
+
+def kept_distribution_pip(logits: torch.Tensor, temperature: torch.Tensor, top_p: torch.Tensor, top_k: torch.Tensor) -> torch.Tensor:
+    """(B,V) fp32: the normalised distribution ``sample_logits_rwkv_pip_compatible`` draws from."""
+    p = _pip_filtered(logits, temperature, top_p, top_k)
+    return p / p.sum(dim=-1, keepdim=True)
+
+
+def worker_sampling_params(temperature: float, top_p: float, top_k: int, frequency_penalty: float, penalty_decay: float,
+                           presence_penalty: float):
+    """The per-slot tensors the worker builds at admission (chirrup/worker.py:611-640): temperature (<= 0 becomes 1.0), top_p,
+    frequency penalty and decay as FP16, presence penalty as fp32, top_k int32 — each (1,1)."""
+    h = lambda v: torch.tensor([[v]], dtype=torch.float16)
+    return dict(temperature=h(temperature if temperature > 0 else 1.0), top_p=h(top_p),
+                top_k=torch.tensor([[top_k]], dtype=torch.int32), frequency_penalty=h(frequency_penalty),
+                penalty_decay=h(penalty_decay), presence_penalty=torch.tensor([[presence_penalty]], dtype=torch.float32))

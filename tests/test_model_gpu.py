@@ -334,8 +334,8 @@ def test_deferred_split_k_reduction_equals_in_kernel_reduction():
 
 
 def test_headline_configuration_properties_7p2B_bsz256():
-    """BASELINE.json configs[2] at full size (7.2B: L32, C4096, 256 decode rows; the oracle cannot run this in seconds):
-    size-independent properties of the step.  (1) Two evaluations from equal states are bit-identical (no atomics, fixed split
+    """BASELINE.json configs[2] at full size (7.2B: L32, C4096, 256 decode rows): size-independent properties of the step (the
+    oracle comparison at this size, 256 greedy steps deep, is tests/test_parity_full_gpu.py).  (1) Two evaluations from equal states are bit-identical (no atomics, fixed split
     order).  (2) Rows are independent and position-free: permuting the batch rows AND addressing the state through the
     matching slot permutation permutes the logits rows bit for bit and leaves every state slot bit-identical.  (3) elapsed
     advances by exactly T per row; untouched spare slots stay zero.  (4) The graph-replayed step equals the eagerly launched one."""

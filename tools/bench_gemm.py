@@ -1,7 +1,10 @@
 """Micro-benchmark of the tcgen05 linear op on the decode-step shapes: back-to-back launches in one CUDA graph, each launch
 streaming a DIFFERENT weight matrix (n_w of them, > L2 in total), so the figure is the warm in-stream cost per launch that the
 model step actually pays (ncu's per-launch times are cold and serialised).
-Usage (GPU box): python tools/bench_gemm.py [--M 256] [--C 4096] [--nw 24] [--json out.json]"""
+--cublas adds, beside each of our launches, the SAME-BOX library bar SURVEY §2a names: torch.nn.functional.linear (cuBLAS /
+cuBLASLt fp16, what Albatross/rwkv7.py:625-630,649,678-679,551 dispatches to) on the same operands in the same graph-replay
+harness — the plain GEMM only; the reference runs its bias / activation / residual as further ATen launches on top of it.
+Usage (GPU box): python tools/bench_gemm.py [--M 256] [--C 4096] [--nw 24] [--cublas] [--json out.json]"""
 import argparse
 import json
 import os
@@ -40,12 +43,14 @@ def main():
     ap.add_argument("--nw", type=int, default=24)
     ap.add_argument("--json", default=None)
     ap.add_argument("--shapes", default="all")
+    ap.add_argument("--cublas", action="store_true")
     a = ap.parse_args()
     M, C, F = a.M, a.C, 4 * a.C
     dev = "cuda"
     shapes = [("cxc", C, C, ops.EPI_NONE), ("cxc_resadd", C, C, ops.EPI_RESADD), ("ffn_key", F, C, ops.EPI_RELU_SQ),
               ("ffn_value", C, F, ops.EPI_RESADD), ("lora_down_128", 128, C, ops.EPI_TANH), ("lora_down_480", 480, C, ops.EPI_SIGMOID),
-              ("lora_up_128", C, 128, ops.EPI_SIGMOID), ("lora_up_480", C, 480, ops.EPI_NONE), ("head", 65536, C, ops.EPI_NONE)]
+              ("lora_down_96", 96, C, ops.EPI_NONE), ("lora_up_128", C, 128, ops.EPI_SIGMOID), ("lora_up_96", C, 96, ops.EPI_SIGMOID),
+              ("lora_up_480", C, 480, ops.EPI_NONE), ("head", 65536, C, ops.EPI_NONE)]
     out = []
     for name, N, K, epi in shapes:
         if a.shapes != "all" and name not in a.shapes.split(","):
@@ -67,6 +72,14 @@ def main():
         us = ms * 1e3 / nw
         rec = {"shape": name, "M": M, "N": N, "K": K, "us_per_launch": round(us, 2),
                "tflops": round(2.0 * M * N * K / us / 1e6, 1), "weight_GBps": round(N * K * 2 / us / 1e3, 1)}
+        if a.cublas:
+            def fn_lib():
+                for W in Ws:
+                    torch.nn.functional.linear(x, W)
+
+            us_lib = time_graph(fn_lib) * 1e3 / nw
+            rec.update({"cublas_us_per_launch": round(us_lib, 2), "cublas_tflops": round(2.0 * M * N * K / us_lib / 1e6, 1),
+                        "ours_over_cublas_time": round(us / us_lib, 3)})
         print(json.dumps(rec), flush=True)
         out.append(rec)
         del Ws
