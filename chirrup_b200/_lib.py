@@ -26,6 +26,7 @@ SIGNATURES: Dict[str, tuple] = {
     "b200_wkv7_forward_seq": (_I, [_I, _I, _I, _I, _P, _L, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "b200_wkv7_forward_one": (_I, [_I, _I, _I, _P, _L, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "b200_tmix_core_fused": (_I, [_I, _I, _I, _I, _P, _L, _I] + [_P] * 17),
+    "b200_tmix_core_chunked": (_I, [_I, _I, _I, _I, _P, _L, _I] + [_P] * 17),
     "b200_spmv_forward": (_I, [_I, _I, _P, _P, _P, _P]),
     "b200_linear_f16": (_I, [_I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P, _I, _P, _L, _P]),
     "b200_linear_workspace_bytes": (_L, [_I, _I]),
@@ -53,7 +54,7 @@ class SampleParams(ctypes.Structure):
     _fields_ = [("slot", _P), ("occurrence", _P), ("presence", _P), ("penalty_decay", _P), ("frequency_penalty", _P),
                 ("presence_penalty", _P), ("temperature", _P), ("top_p", _P), ("top_k", _P), ("forbidden", _P),
                 ("max_forbidden", _I), ("no_penalty", _P), ("n_no_penalty", _I), ("seed", _c.c_ulonglong),
-                ("step", _c.c_ulonglong), ("kept", _P)]
+                ("step", _c.c_ulonglong), ("kept", _P), ("mode", _I)]
 
 
 def header_symbols() -> List[str]:

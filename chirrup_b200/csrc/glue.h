@@ -53,6 +53,9 @@ struct WkvFusedArgs {
 };
 int launch_wkv7_fused(const WkvFusedArgs& a, void* state, long state_slot_stride, int n_slots, cudaStream_t stream,
                       bool pdl = false);
+// wkv7_chunk.cu: the same fused TMix core with the recurrence in its chunked tensor-core form (prefill; tolerance-level parity)
+int launch_wkv7_chunk(const WkvFusedArgs& a, void* state, long state_slot_stride, int n_slots, cudaStream_t stream,
+                      bool pdl = false);
 int launch_wkv7_seq(int B, int T, int C, int H, void* state, long state_slot_stride, int n_slots, const void* r, const void* w,
                     const void* k, const void* v, const void* a, const void* b, void* y, const int* elapsed_t,
                     const int* slot_idx, cudaStream_t stream, bool pdl = false);

@@ -111,6 +111,7 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
     // Programmatic dependent launch for every kernel after the first (the first one orders the step after whatever the caller
     // enqueued before it); every kernel of the step calls griddepcontrol.wait before touching its predecessors' outputs.
     const bool pdl = getenv("B200_NO_PDL") == nullptr;
+    const bool wkv_sequential = getenv("B200_WKV_SEQUENTIAL") != nullptr;
     const bool no_group = getenv("B200_NO_PAIR") != nullptr;  // A/B switch: the one-CTA-per-tile GEMM path of gemm.cu
 #define RUN(call)                                                                                     \
     do {                                                                                              \
@@ -196,7 +197,12 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             fa.k_k = w[B200_LW_K_K]; fa.k_a = w[B200_LW_K_A]; fa.r_k = w[B200_LW_R_K];
             fa.ln_w = w[B200_LW_LNX_W]; fa.ln_b = w[B200_LW_LNX_B];
             fa.out = ws.yg; fa.elapsed_t = elapsed; fa.slot_idx = slot_idx;
-            RUN_T(8, launch_wkv7_fused(fa, s1 + l * s1_layer_stride, (long)C * 64, n_slots, st, pdl));
+            // prefill (T >= 32): the chunked tensor-core form of the recurrence; decode and short T: the sequential kernels,
+            // bit-identical to the reference kernel (B200_WKV_SEQUENTIAL=1 forces them everywhere)
+            if (T >= 32 && !wkv_sequential)
+                RUN_T(8, launch_wkv7_chunk(fa, s1 + l * s1_layer_stride, (long)C * 64, n_slots, st, pdl));
+            else
+                RUN_T(8, launch_wkv7_fused(fa, s1 + l * s1_layer_stride, (long)C * 64, n_slots, st, pdl));
         } else {
             TmixPrepArgs pa;
             pa.M = (int)M; pa.C = C;

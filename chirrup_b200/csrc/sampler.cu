@@ -16,6 +16,14 @@
 //   3. the draw is u * (kept mass), located in the same scan as (key class, ordinal); a last pass over the row finds the
 //      ordinal-th element with that key (ties are broken in thread-major order, which torch.sort leaves unspecified).
 //
+// mode 1 is the sampler the worker ACTUALLY imports (chirrup/worker.py:12: `sample_logits_rwkv_pip_compatible as
+// sample_logits_real_batch`, chirrup/utils/samplers.py:171-255): softmax WITHOUT temperature; top-p keeps every token whose
+// probability is >= the probability at the first sorted position where the cumulative sum reaches top_p (whole tie classes
+// stay: a cutoff by VALUE); top-k keeps sort rank < k; THEN probs ** (1/T); multinomial.  In the histogram formulation: the
+// boundary class is the first (descending) whose class mass brings the T = 1 cumulative mass to >= top_p * Z, it is kept
+// whole unless top-k cuts into it, and the draw uses masses exp((l - max) / T) over the kept set (inv_T = fp16(1 / T), the
+// reference's tensors are fp16).  mode 0 is the single-sort sampler of samplers.py:98-168 described above.
+//
 // Greedy rows (top_k == 1, top_p == 0 or temperature <= 0) take the arg-max with the lowest index, like b200_argmax_f16.
 // The penalised logits are written back in place (fp32 math, one fp16 rounding per reference op), like the reference's decode_out.
 #include "common.cuh"
@@ -138,6 +146,7 @@ struct SampleArgs {
     u64 seed, step;
     int* kept;
     int* out;
+    int mode;   // 0: samplers.py:98-168 (temperature first, nucleus by cumulative mass); 1: samplers.py:171-255 (rwkv pip)
 };
 
 constexpr int NKEY = 65536;          // distinct fp16 bit patterns
@@ -215,11 +224,21 @@ __global__ void __launch_bounds__(ST, 1) sample_rows_kernel(const SampleArgs a) 
 
     if (!greedy) {
         const uint32_t kmin_all = 0xFFFFu - (uint32_t)block_max_u64((u64)(0xFFFFu - kmin), s);
-        const float inv_t = 1.0f / temp;
-        const float xm = val_of_key(kmax) * inv_t;
-        // unnormalised probability exp(l/T - max/T) of a key as 32-bit fixed point (1.0 -> 2^32 - 1, exp(-inf) -> 0)
+        const bool pip = a.mode == 1;
+        const float inv_t = pip ? __half2float(__float2half_rn(1.0f / temp)) : 1.0f / temp;   // :244 on fp16 tensors
+        const float vmax = val_of_key(kmax);
+        const float xm = vmax * inv_t;
+        // unnormalised probability exp(l/T - max/T) of a key as 32-bit fixed point (1.0 -> 2^32 - 1, exp(-inf) -> 0): what the
+        // draw uses in both modes, and what the filters use in mode 0
         auto mass_of_key = [&](uint32_t key) -> u64 {
             const float e = exp2f((val_of_key(key) * inv_t - xm) * 1.4426950408889634f);
+            return (u64)__float2uint_rd(e * FIX_ONE);
+        };
+        // mode 1 filters on the UNtempered distribution softmax(logits) (samplers.py:198)
+        const bool two_mass = pip && inv_t != 1.0f;
+        auto fmass_of_key = [&](uint32_t key) -> u64 {
+            if (!two_mass) return mass_of_key(key);
+            const float e = exp2f((val_of_key(key) - vmax) * 1.4426950408889634f);
             return (u64)__float2uint_rd(e * FIX_ONE);
         };
         const uint4 rnd = philox4x32(make_uint4((uint32_t)row, (uint32_t)a.step, (uint32_t)(a.step >> 32), 0u),
@@ -232,6 +251,7 @@ __global__ void __launch_bounds__(ST, 1) sample_rows_kernel(const SampleArgs a) 
             const u64 m1 = mass_of_key(kmax);
             const u64 k_eff = top_k > 0 ? (u64)min(top_k, V) : (u64)V;
             u64 take = top_p < 1.0f ? (u64)((double)V * (double)top_p) : (u64)V;  // cumsum_j = (j+1)/V <= top_p
+            if (pip) take = (u64)V;                                               // one tie class: the cutoff value keeps it whole
             take = take < k_eff ? take : k_eff;
             take = take ? take : 1ull;
             (void)m1;
@@ -242,7 +262,7 @@ __global__ void __launch_bounds__(ST, 1) sample_rows_kernel(const SampleArgs a) 
             // ---- histogram scan in DESCENDING key order: thread t owns words w_hi, w_hi-1, .., w_hi-63 (keys 2w+1, 2w)
             const int lane = t & 31;
             const uint32_t w_hi = HWORDS - 1 - t * WPT;
-            u64 cnt = 0ull, mass = 0ull;
+            u64 cnt = 0ull, mass = 0ull, dmass = 0ull;   // mass: what the filters see; dmass: what the draw sees (mode 1, T != 1)
 #pragma unroll 4
             for (int i = 0; i < WPT; i++) {
                 const uint32_t w = w_hi - ((i + lane) & (WPT - 1));  // rotated per lane: conflict-free; sums do not care
@@ -250,8 +270,12 @@ __global__ void __launch_bounds__(ST, 1) sample_rows_kernel(const SampleArgs a) 
                 if (word) {
                     const uint32_t c1 = word >> 16, c0 = word & 0xFFFFu;
                     cnt += c1 + c0;
-                    if (c1) mass += c1 * mass_of_key(2 * w + 1);
-                    if (c0) mass += c0 * mass_of_key(2 * w);
+                    if (c1) mass += c1 * fmass_of_key(2 * w + 1);
+                    if (c0) mass += c0 * fmass_of_key(2 * w);
+                    if (two_mass) {
+                        if (c1) dmass += c1 * mass_of_key(2 * w + 1);
+                        if (c0) dmass += c0 * mass_of_key(2 * w);
+                    }
                 }
             }
             if (t == 0) {
@@ -259,31 +283,40 @@ __global__ void __launch_bounds__(ST, 1) sample_rows_kernel(const SampleArgs a) 
                 s.c_prime = 0u;
                 s.mass_prime = 0ull;
             }
-            u64 n_valid, Z;
+            u64 n_valid, Z, Zd;
             const u64 pc = block_excl_scan(cnt, n_valid, s);
             const u64 pm = block_excl_scan(mass, Z, s);
+            const u64 pd = two_mass ? block_excl_scan(dmass, Zd, s) : pm;   // draw-mass prefix
+            if (!two_mass) dmass = mass, Zd = Z;
             const u64 k_eff = top_k > 0 ? min((u64)top_k, n_valid) : n_valid;
-            const u64 P = top_p < 1.0f ? (u64)((double)Z * (double)top_p) : ~0ull;
-            if (t == 0) s.c_star = n_valid, s.m_star = Z;
+            u64 P = top_p < 1.0f ? (u64)((double)Z * (double)top_p) : ~0ull;
+            if (pip && P == 0ull) P = 1ull;
+            if (t == 0) s.c_star = n_valid, s.m_star = Zd;
             __syncthreads();
-            // the first key (descending) whose whole class no longer fits: rank >= k_eff or cumulative mass > P
-            if (!(pc > k_eff || pm > P) && (pc + cnt > k_eff || pm + mass > P)) {
-                u64 cc = pc, cm = pm;
+            // the first key (descending) at which a filter bites.  mode 0: the class no longer fits whole — rank >= k_eff or
+            // cumulative mass > P.  mode 1: rank >= k_eff, or the class brings the cumulative mass to >= P (it is then the LAST
+            // class kept, and kept whole: cutoff by value, samplers.py:209-216)
+            const bool before = pip ? (pc > k_eff || pm >= P) : (pc > k_eff || pm > P);
+            const bool within = pip ? (pc + cnt > k_eff || pm + mass >= P) : (pc + cnt > k_eff || pm + mass > P);
+            if (!before && within) {
+                u64 cc = pc, cm = pm, cd = pd;
                 for (int i = 0; i < 2 * WPT; i++) {
                     const uint32_t key = 2 * w_hi + 1 - i;
                     const u64 c = hist_count(hist, key);
                     if (!c) continue;
-                    const u64 m1 = mass_of_key(key);
-                    if (cc + c > k_eff || cm + c * m1 > P) {
+                    const u64 m1 = fmass_of_key(key);
+                    if (cc + c > k_eff || (pip ? cm + c * m1 >= P : cm + c * m1 > P)) {
                         s.kprime = key;
                         s.c_prime = (uint32_t)c;
-                        s.mass_prime = m1;
+                        s.mass_prime = pip ? mass_of_key(key) : m1;     // per-element DRAW mass of the boundary class
                         s.c_star = cc;
-                        s.m_star = cm;
+                        s.m_star = pip ? cd : cm;                        // draw mass of the classes kept whole above it
+                        s.b32 = (pip && !(cc + c > k_eff)) ? 1u : 0u;    // mode 1, nucleus boundary: the whole class stays
                         break;
                     }
                     cc += c;
                     cm += c * m1;
+                    if (two_mass) cd += c * mass_of_key(key); else cd = cm;
                 }
             }
             __syncthreads();
@@ -291,9 +324,13 @@ __global__ void __launch_bounds__(ST, 1) sample_rows_kernel(const SampleArgs a) 
             const u64 c_star = s.c_star, m_star = s.m_star, mass_prime = s.mass_prime;
             u64 take = 0ull;
             if (kprime) {  // partially kept class: equal masses, so `take` of its elements
-                const u64 rem_p = mass_prime ? (P - m_star) / mass_prime : (u64)s.c_prime;
                 take = min((u64)s.c_prime, k_eff - c_star);
-                take = take < rem_p ? take : rem_p;
+                if (pip) {
+                    if (s.b32) take = (u64)s.c_prime;
+                } else {
+                    const u64 rem_p = mass_prime ? (P - m_star) / mass_prime : (u64)s.c_prime;
+                    take = take < rem_p ? take : rem_p;
+                }
                 if (c_star == 0ull && take == 0ull) take = 1ull;  // min_tokens_to_keep = 1 (samplers.py:105, :145-146)
             }
             const u64 m_kept = m_star + take * mass_prime;
@@ -302,8 +339,8 @@ __global__ void __launch_bounds__(ST, 1) sample_rows_kernel(const SampleArgs a) 
             const u64 target = __umul64hi(r64, m_kept);
             if (target >= m_star) {
                 if (t == 0) s.kd = kprime, s.ord = mass_prime ? (target - m_star) / mass_prime : 0ull;
-            } else if (pm <= target && target < pm + mass) {
-                u64 cm = pm;
+            } else if (pd <= target && target < pd + dmass) {
+                u64 cm = pd;
                 for (int i = 0; i < 2 * WPT; i++) {
                     const uint32_t key = 2 * w_hi + 1 - i;
                     const u64 c = hist_count(hist, key);
@@ -378,7 +415,7 @@ extern "C" int b200_sample_f16(int rows, int V, void* logits, long ld, const b20
     if (V > ST * SCH * 8) return B200_ERR_UNSUPPORTED;
     if ((p->occurrence == nullptr) != (p->presence == nullptr)) return B200_ERR_BAD_ARG;
     if (p->occurrence && (!p->penalty_decay || !p->frequency_penalty || !p->presence_penalty)) return B200_ERR_BAD_ARG;
-    if (p->max_forbidden < 0 || p->max_forbidden > ST || p->n_no_penalty < 0) return B200_ERR_BAD_ARG;
+    if (p->max_forbidden < 0 || p->max_forbidden > ST || p->n_no_penalty < 0 || p->mode < 0 || p->mode > 1) return B200_ERR_BAD_ARG;
     if ((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(p->occurrence) | reinterpret_cast<uintptr_t>(p->presence)) & 15)
         return B200_ERR_BAD_ARG;
     if (rows == 0) return 0;
@@ -389,7 +426,7 @@ extern "C" int b200_sample_f16(int rows, int V, void* logits, long ld, const b20
     a.temp = p->temperature; a.top_p = p->top_p; a.top_k = p->top_k;
     a.forbidden = p->max_forbidden > 0 ? p->forbidden : nullptr; a.max_forbidden = p->max_forbidden;
     a.no_penalty = p->no_penalty; a.n_no_penalty = p->no_penalty ? p->n_no_penalty : 0;
-    a.seed = p->seed; a.step = p->step; a.kept = p->kept; a.out = out;
+    a.seed = p->seed; a.step = p->step; a.kept = p->kept; a.out = out; a.mode = p->mode;
     const size_t smem = (size_t)HWORDS * 4;  // the per-key histogram
     cudaError_t e = cudaFuncSetAttribute(sample_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;

@@ -114,7 +114,10 @@ class Task:                                                 # core_structure.py:
         return RequestStatus.is_finished(self.request_status)
 
     def is_greedy(self) -> bool:
-        return self.top_k == 1 or self.temperature == 0 or self.top_p == 0
+        """Rows the sampler resolves to the arg-max: top_k == 1 or top_p == 0 (the nucleus cutoff is then the top probability).
+        temperature <= 0 is NOT greedy here: the worker replaces it by 1.0 at admission and still samples with the request's
+        top_p / top_k (chirrup/worker.py:611-613)."""
+        return self.top_k == 1 or self.top_p == 0
 
 
 @dataclass
@@ -173,6 +176,8 @@ class Worker:
         self._step_bufs = None
         self.pipeline = True
         self.sample_seed = 0x5EED0000 + sum(map(ord, str(worker_id)))
+        self.no_penalty_token_ids = (33, 10, 49, 50, 51, 52, 53, 54, 55, 56, 57, 58)   # worker.py:173: "!", "\n", digits
+        self._no_penalty_dev = None
         self._stop = False
 
     # ------------------------------------------------------------------ init
@@ -288,9 +293,10 @@ class Worker:
             return
         greedy = t.is_greedy()
         h = self._par_host
-        h[0, pos] = 1.0 if greedy else t.temperature
-        h[1, pos] = 1.0 if greedy else t.top_p
-        h[2, pos], h[3, pos], h[4, pos] = t.penalty_decay, t.frequency_penalty, t.presence_penalty
+        f16 = lambda v: float(torch.tensor(v, dtype=torch.float16))   # the worker keeps these as fp16 tensors (worker.py:611-635)
+        h[0, pos] = 1.0 if greedy else f16(t.temperature if t.temperature > 0 else 1.0)   # worker.py:611-613
+        h[1, pos] = 1.0 if greedy else f16(t.top_p)
+        h[2, pos], h[3, pos], h[4, pos] = f16(t.penalty_decay), f16(t.frequency_penalty), t.presence_penalty   # presence: fp32 (:636-640)
         h[5, pos] = 1.0 if greedy else float(max(t.top_k, 0))
         self._occurrence[pos].zero_()
         self._presence[pos].zero_()
@@ -331,9 +337,13 @@ class Worker:
             if not logits.is_contiguous():
                 logits = logits.contiguous()
             pd = self._par_dev
+            if self._no_penalty_dev is None:
+                self._no_penalty_dev = torch.tensor(self.no_penalty_token_ids, dtype=torch.int32, device=self.device)
+            # mode 1: the sampler the reference worker imports (worker.py:12 -> samplers.py:171-255); tokens in
+            # no_penalty_token_ids do not accumulate a frequency penalty (worker.py:508)
             ids = ops.sample(logits, pd[0], pd[1], self._topk_dev, slot=slot, occurrence=self._occurrence, presence=self._presence,
                              penalty_decay=pd[2], frequency_penalty=pd[3], presence_penalty=pd[4], forbidden=forb,
-                             seed=self.sample_seed, step=self.steps["decode"])
+                             no_penalty=self._no_penalty_dev, seed=self.sample_seed, step=self.steps["decode"], mode=1)
         return ids
 
     def _sample_host(self, rows: List[int], logits: torch.Tensor) -> List[int]:
@@ -343,6 +353,7 @@ class Worker:
             t = self.slots[p].task
             if t is None or t.is_greedy():
                 continue
+            temperature = t.temperature if t.temperature > 0 else 1.0
             if self._occ_host is None:
                 self._occ_host = torch.zeros((self.batch_size, logits.shape[1]), dtype=torch.float32)
             occ = self._occ_host[p]
@@ -350,7 +361,7 @@ class Worker:
             if t.forbidden_tokens:
                 lg[torch.tensor(t.forbidden_tokens)] -= 1e10
             lg = lg - t.presence_penalty * (occ > 0).float() - t.frequency_penalty * occ
-            probs = torch.softmax(lg / max(t.temperature, 1e-6), dim=-1)
+            probs = torch.softmax(lg / temperature, dim=-1)
             sp, si = torch.sort(probs, descending=True)
             keep = torch.cumsum(sp, 0) <= t.top_p
             if t.top_k > 0:
@@ -451,16 +462,17 @@ class Worker:
             t = s.task
             if t is None or t is not rec["tasks"][i]:
                 continue
+            delivered += 1
+            if tok in t.stop_tokens:                                             # worker.py:488-490: a stop token ends the request
+                self._finish(p, RequestStatus.FINISHED_STOPPED)                  # and is neither recorded nor sent to the client
+                continue
             s.next_token = tok
             s.category = StateCategory.FORWARD_ONE_DECODE
             t.generated_tokens.append(tok)
-            delivered += 1
             if t.output_queue is not None:
                 t.output_queue.put_nowait(("token", tok, self.tokenizer.decode([tok]),
                                            rec["logits"][j] if (t.return_logits and rec["logits"] is not None) else None))
-            if tok in t.stop_tokens:
-                self._finish(p, RequestStatus.FINISHED_STOPPED)
-            elif t.max_tokens is not None and len(t.generated_tokens) >= t.max_tokens:
+            if t.max_tokens is not None and len(t.generated_tokens) >= t.max_tokens:
                 self._finish(p, RequestStatus.FINISHED_LENGTH_CAPPED)
         self.steps["decode_tokens"] += delivered
         return delivered

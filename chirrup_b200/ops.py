@@ -130,9 +130,11 @@ def argmax(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
     return out
 
 
-def tmix_core_fused(state, r, w, k, v, a, g, vgate, v_first, k_k, k_a, r_k, ln_w, ln_b, elapsed_t, slot_idx=None, out=None):
+def tmix_core_fused(state, r, w, k, v, a, g, vgate, v_first, k_k, k_a, r_k, ln_w, ln_b, elapsed_t, slot_idx=None, out=None,
+                    chunked=False):
     """The fused TMix core (``b200_tmix_core_fused``): inputs (B,T,C) fp16, per-channel vectors (C,), state (n_slots,H,64,64)
-    updated in place; ``vgate`` / ``v_first`` None on layer 0.  Returns (B,T,C)."""
+    updated in place; ``vgate`` / ``v_first`` None on layer 0.  Returns (B,T,C).  ``chunked=True``: the tensor-core chunked
+    prefill form (``b200_tmix_core_chunked``), same arguments, tolerance-level agreement with the sequential kernel."""
     B, T, C = r.shape
     H = C // HEAD
     if out is None:
@@ -142,10 +144,11 @@ def tmix_core_fused(state, r, w, k, v, a, g, vgate, v_first, k_k, k_a, r_k, ln_w
     p = lambda t: 0 if t is None else t.contiguous().data_ptr()
     n_slots = state.shape[0]
     stride = state.stride(0) if n_slots > 1 else C * HEAD
-    rc = _lib.lib().b200_tmix_core_fused(B, T, C, H, state.data_ptr(), stride, n_slots, p(r), p(w), p(k), p(v), p(a), p(g),
-                                         p(vgate), p(v_first), p(k_k), p(k_a), p(r_k), p(ln_w), p(ln_b), out.data_ptr(),
-                                         elapsed_t.data_ptr(), p(slot_idx), _stream(r))
-    _lib.check(rc, "b200_tmix_core_fused")
+    fn = _lib.lib().b200_tmix_core_chunked if chunked else _lib.lib().b200_tmix_core_fused
+    rc = fn(B, T, C, H, state.data_ptr(), stride, n_slots, p(r), p(w), p(k), p(v), p(a), p(g),
+            p(vgate), p(v_first), p(k_k), p(k_a), p(r_k), p(ln_w), p(ln_b), out.data_ptr(),
+            elapsed_t.data_ptr(), p(slot_idx), _stream(r))
+    _lib.check(rc, "b200_tmix_core_chunked" if chunked else "b200_tmix_core_fused")
     return out
 
 
@@ -186,12 +189,15 @@ def sample(logits: torch.Tensor, temperature: Optional[torch.Tensor] = None, top
            occurrence: Optional[torch.Tensor] = None, presence: Optional[torch.Tensor] = None,
            penalty_decay: Optional[torch.Tensor] = None, frequency_penalty: Optional[torch.Tensor] = None,
            presence_penalty: Optional[torch.Tensor] = None, forbidden: Optional[torch.Tensor] = None,
-           no_penalty: Optional[torch.Tensor] = None, seed: int = 0, step: int = 0, return_kept: bool = False):
+           no_penalty: Optional[torch.Tensor] = None, seed: int = 0, step: int = 0, return_kept: bool = False,
+           mode: int = 0):
     """One decode sampling step (``b200_sample_f16``): the worker's penalty block (``chirrup/worker.py:713-740``), its sampler
     (``chirrup/utils/samplers.py:98-168``) and the penalty update of the drawn token (``worker.py:527-547``) in one kernel.
     ``logits`` fp16 (rows, V) is penalised IN PLACE; per-slot parameter tensors are 1-D (n_slots) — fp32, ``top_k`` int32 —
     indexed by ``slot`` (int32 (rows), default: row index); ``occurrence`` / ``presence`` fp32 (n_slots, V) are updated in place;
-    ``forbidden`` int32 (rows, F) padded with -1.  Returns int32 (rows) token ids (and the kept-set sizes if asked)."""
+    ``forbidden`` int32 (rows, F) padded with -1.  ``mode`` 0: the single-sort sampler (``samplers.py:98-168``); 1: the one the
+    worker imports, ``sample_logits_rwkv_pip_compatible`` (``samplers.py:171-255``, ``worker.py:12``).  Returns int32 (rows)
+    token ids (and the kept-set sizes if asked)."""
     _req(logits, "logits")
     if logits.dim() != 2 or logits.stride(1) != 1:
         raise ValueError("logits must be (rows, V) with unit inner stride")
@@ -225,6 +231,7 @@ def sample(logits: torch.Tensor, temperature: Optional[torch.Tensor] = None, top
     P.no_penalty = ptr(no_penalty, "no_penalty", torch.int32)
     P.n_no_penalty = 0 if no_penalty is None else no_penalty.numel()
     P.seed, P.step = seed & (2 ** 64 - 1), step & (2 ** 64 - 1)
+    P.mode = int(mode)
     kept = torch.empty((rows,), dtype=torch.int32, device=dev) if return_kept else None
     P.kept = kept.data_ptr() if kept is not None else None
     out = torch.empty((rows,), dtype=torch.int32, device=dev)

@@ -35,7 +35,7 @@ _LW_ORDER = [
 ]
 
 
-_STEP_ENV = ("B200_UNFUSED_TMIX", "B200_NO_PDL", "B200_NO_PAIR", "B200_NO_DEFER", "B200_WKV_GENERIC", "B200_CHAIN")
+_STEP_ENV = ("B200_UNFUSED_TMIX", "B200_NO_PDL", "B200_NO_PAIR", "B200_NO_DEFER", "B200_WKV_GENERIC", "B200_CHAIN", "B200_WKV_SEQUENTIAL")
 
 
 def _stream(dev) -> int:

@@ -65,6 +65,19 @@ int b200_tmix_core_fused(int B, int T, int C, int H, void* state, long state_slo
                          const void* ln_b, void* out, const int* elapsed_t, const int* slot_idx, void* stream);
 
 /*
+ * The same fused TMix core for PREFILL (T >= 16 pays off): the WKV-7 recurrence evaluated 16 tokens at a time in its chunked
+ * (WY / UT-transform) form on the tensor cores — fp16 operands rescaled around the middle of each chunk by the per-channel
+ * cumulative decays (the elapsed_t dither folded into every token's decay), fp32 accumulation, state kept in fp32 for the
+ * whole launch and rounded to fp16 once (csrc/wkv7_chunk.cu).  The reference has only the sequential T loop
+ * (Albatross/cuda/rwkv7_state_fwd_fp16.cu:56-82); agreement with it is to its own fp16 noise, not bit for bit — the
+ * sequential kernels (b200_tmix_core_fused) remain the bit-exact mode.  Same arguments as b200_tmix_core_fused.
+ */
+int b200_tmix_core_chunked(int B, int T, int C, int H, void* state, long state_slot_stride, int n_slots, const void* r,
+                           const void* w, const void* k, const void* v, const void* a, const void* g, const void* vgate,
+                           const void* v_first, const void* k_k, const void* k_a, const void* r_k, const void* ln_w,
+                           const void* ln_b, void* out, const int* elapsed_t, const int* slot_idx, void* stream);
+
+/*
  * out[c] = sum_d vec[d] * mat[d*C + c], skipping rows with vec[d] == 0 (ReLU^2 sparsity of the FFN key).
  * vec (D) fp16, mat (D,C) fp16 row-major, out (C) fp16 — overwritten (no pre-zeroing needed, unlike the reference).
  * fp32 accumulation in a fixed order: deterministic, one rounding.
@@ -198,6 +211,11 @@ typedef struct b200_sample_params {
     int n_no_penalty;
     unsigned long long seed, step;
     int* kept;                       /* optional int32 (rows): size of the kept set (tests / debugging) */
+    int mode;                        /* 0: samplers.py:98-168 as described above.  1: the sampler chirrup/worker.py:12 imports,
+                                      * sample_logits_rwkv_pip_compatible (samplers.py:171-255): softmax WITHOUT temperature;
+                                      * top-p keeps every token whose probability is >= the probability at the first sorted
+                                      * position where the cumulative sum reaches top_p (ties at the cutoff all stay); top-k on
+                                      * the sort rank; then probs ** fp16(1 / temperature); draw proportionally */
 } b200_sample_params;
 int b200_sample_f16(int rows, int V, void* logits, long ld, const b200_sample_params* params, int* out, void* stream);
 

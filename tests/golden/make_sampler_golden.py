@@ -86,5 +86,56 @@ def main():
         print(name, "ok; kept per row:", (dist > 0).sum(1).tolist())
 
 
+def main_pip():
+    """The sampler the worker imports (chirrup/worker.py:12 -> samplers.py:171-255) with the parameter tensors in the dtypes the
+    worker builds at admission (worker.py:611-640: temperature / top_p / frequency penalty / decay FP16, presence fp32)."""
+    for name, B, V, scale, T, P, K in CASES:
+        g = torch.Generator().manual_seed(sum(map(ord, name)) + 7)
+        logits = (torch.randn(B, V, generator=g) * scale).half()
+        if T is None:
+            temp = torch.tensor([[1.0], [0.7], [1.5], [1.0], [0.3], [1.0]])
+            top_p = torch.tensor([[1.0], [0.8], [0.95], [0.3], [1.0], [0.6]])
+            top_k = torch.tensor([[0], [20], [0], [5], [100], [1]], dtype=torch.int32)
+        else:
+            temp, top_p, top_k = torch.full((B, 1), T), torch.full((B, 1), P), torch.full((B, 1), K, dtype=torch.int32)
+        temp, top_p = temp.half(), top_p.half()
+        occ, alpha = torch.zeros(B, V), torch.zeros(B, V)
+        decay, freq, pres = torch.full((B, 1), 0.996).half(), torch.full((B, 1), 0.3).half(), torch.full((B, 1), 0.4)
+        hist = torch.randint(0, V, (B, 12), generator=g)
+        for b in range(B):
+            for t in hist[b].tolist():
+                occ[b, t] += 1.0
+                alpha[b, t] = pres[b, 0]
+        forbidden = [[int(x) for x in torch.randint(0, V, (2,), generator=g)] for _ in range(B)]
+        ref_logits, ref_occ = logits.clone(), occ.clone()
+        for b in range(B):
+            for t in forbidden[b]:
+                ref_logits[b][t] -= 1e10
+        ref_occ[:, :] *= decay                                   # worker.py:725 with its fp16 decay tensor
+        ref_logits -= (alpha + ref_occ * freq)                   # :726-729 with its fp16 frequency tensor
+        o_logits, o_occ = logits.clone(), occ.clone()
+        SO.penalise(o_logits, o_occ, alpha, decay, freq, forbidden)
+        assert torch.equal(o_logits, ref_logits) and torch.equal(o_occ, ref_occ)
+        draws = []
+        for seed in range(8):
+            torch.manual_seed(seed)
+            ref_tok = R.sample_logits_rwkv_pip_compatible(ref_logits.clone(), temp, top_p, top_k)
+            torch.manual_seed(seed)
+            my_tok = SO.sample_logits_rwkv_pip_compatible(o_logits.clone(), temp, top_p, top_k)
+            assert torch.equal(ref_tok, my_tok), (name, seed)
+            draws.append(ref_tok.numpy())
+        dist = SO.kept_distribution_pip(o_logits, temp, top_p, top_k)
+        for d in draws:
+            assert all(dist[b, d[b]] > 0 for b in range(B))
+        np.savez_compressed(os.path.join(OUT, f"samplerpip_{name}.npz"), logits=logits.numpy(), occ=occ.numpy(), alpha=alpha.numpy(),
+                            decay=decay.numpy(), freq=freq.numpy(), pres=pres.numpy(), forbidden=np.array(forbidden, dtype=np.int32),
+                            temp=temp.numpy(), top_p=top_p.numpy(), top_k=top_k.numpy(), pen_logits=ref_logits.numpy(),
+                            pen_occ=ref_occ.numpy(), draws=np.stack(draws), dist=dist.numpy())
+        print("pip", name, "ok; kept per row:", (dist > 0).sum(1).tolist())
+
+
 if __name__ == "__main__":
-    main()
+    import sys
+    if "--pip-only" not in sys.argv:
+        main()
+    main_pip()

@@ -160,3 +160,33 @@ def test_async_engine_roundtrip_with_toy_model():
     outs, reasons = asyncio.run(main())
     assert outs == [[(i + 2 + k) % 50 for k in range(3)] for i in range(6)]
     assert all(r == FinishReason.LENGTH for r in reasons)
+
+
+def test_stop_token_is_neither_recorded_nor_streamed():
+    """chirrup/worker.py:488-490: on a stop token the request finishes WITHOUT appending it to generated_tokens or emitting a
+    token event; it does not count toward max_tokens either."""
+    w = make_worker(bsz=4)
+    s = Sink()
+    t = Task(prefill_tokens=[5], output_queue=s, top_k=1, max_tokens=4, stop_tokens=[9])
+    w.task_queue.put(t)
+    for _ in range(50):
+        w.step()
+        if not w.busy():
+            break
+    assert t.generated_tokens == [6, 7, 8] and t.request_status == RequestStatus.FINISHED_STOPPED
+    assert [e[1] for e in s.items if e[0] == "token"] == [6, 7, 8]
+    assert s.items[-1][0] == "finish" and s.items[-1][1] == FinishReason.STOP
+    # the cap is on delivered tokens: with max_tokens = 3 the request ends by LENGTH before the stop token is ever sampled
+    s2 = Sink()
+    t2 = Task(prefill_tokens=[5], output_queue=s2, top_k=1, max_tokens=3, stop_tokens=[9])
+    w.task_queue.put(t2)
+    for _ in range(50):
+        w.step()
+        if not w.busy():
+            break
+    assert t2.generated_tokens == [6, 7, 8] and s2.items[-1][1] == FinishReason.LENGTH
+
+
+def test_greedy_classification_follows_the_reference_worker():
+    assert Task(top_k=1).is_greedy() and Task(top_p=0.0).is_greedy()
+    assert not Task(temperature=0.0).is_greedy()          # worker.py:611-613: temperature <= 0 becomes 1.0 and still samples
