@@ -39,6 +39,12 @@ def parse():
     ap.add_argument("--geom", default="7.2B")
     ap.add_argument("--bsz", type=int, default=256)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--config", default="decode", choices=["decode", "prefill", "engine", "migration"],
+                    help="decode: BASELINE configs[2] (the headline, default); prefill: configs[3] (7.2B, 32 x 4096-token prompts, "
+                         "chunked WKV, state-cache reuse); engine: configs[2] through the AsyncEngineCore worker loop, one worker "
+                         "PROCESS per GPU on one task queue; migration: configs[4] (13.3B, 512 slots, P2P slot migration, 2 GPUs)")
+    ap.add_argument("--no-engine", action="store_true", help="decode config: leave out the engine-level (worker loop) phase")
+    ap.add_argument("--engine-requests", type=int, default=512, help="requests per worker in the engine phase")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=100.0, help="reference arm: stop timing steps after this many seconds")
     ap.add_argument("--skip-configs0", action="store_true", help="reference arm: leave out the BASELINE configs[0] figure")
@@ -320,10 +326,11 @@ def run_ours(a, rank, world, device):
             graph = None
     do_step = graph.replay if graph is not None else step
 
+    from chirrup_b200 import dist_util
+
     def barrier():
         torch.cuda.synchronize()
-        if world > 1:
-            torch.distributed.barrier()
+        dist_util.barrier()
         torch.cuda.synchronize()
 
     for _ in range(a.warmup):
@@ -340,16 +347,17 @@ def run_ours(a, rank, world, device):
     barrier()
 
     # ---- end to end through the public API with host buffers (the call Chirrup's worker makes, chirrup/worker.py:704)
-    host_tok = torch.randint(1, V, (B, 1), generator=gen).to(torch.int32).pin_memory()
     host_out = torch.empty((B,), dtype=torch.int32).pin_memory()
+    e2e_tokens = [torch.randint(1, V, (B, 1), generator=gen).tolist()]
 
     def e2e_step():
-        # public API, host token ids in (pinned (B,1) int32): H2D copy + RWKV_x070.forward_seq_batch_seperate (C ABI)
-        lg = m.forward_seq_batch_seperate(host_tok, state)
+        # the call Chirrup's worker makes (chirrup/worker.py:690-704): token ids as a Python List[List[int]] — torch.tensor(list)
+        # + pageable H2D inside the API — then logits -> greedy sample -> D2H of the ids -> the next step's list
+        lg = m.forward_seq_batch_seperate(e2e_tokens[0], state)
         ops.argmax(lg, out=nxt)
         host_out.copy_(nxt, non_blocking=True)                                  # D2H of the sampled ids
         torch.cuda.current_stream().synchronize()
-        host_tok.view(-1).copy_(host_out)                                       # next step's input comes from the host side
+        e2e_tokens[0] = [[t] for t in host_out.tolist()]                        # next step's input comes from the host side
 
     for _ in range(max(3, a.warmup, getattr(m, "graph_after", 0) + 2)):   # past the point where the API captures its step graph
         e2e_step()
@@ -362,12 +370,153 @@ def run_ours(a, rank, world, device):
     barrier()
 
     wkv_s = time_wkv_kernel(m, geom, state, B) if rank == 0 else {"fused": 0.0, "plain": 0.0}
-    times = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=device)
-    if world > 1:
-        torch.distributed.all_reduce(times, op=torch.distributed.ReduceOp.MAX)
-    ms, e2e_ms = times.tolist()
+    # in-step figure: the same step graph captured with the fused WKV launches knocked out (model.cu B200_DEBUG_SKIP=8; results
+    # are garbage, only the time is read): step - knocked-out step = what the 32 WKV launches cost INSIDE the step, PDL overlap,
+    # L2 state of the neighbours and clocks under load included (an upper bound: skipping also breaks the PDL chain)
+    wkv_in_step_s = None
+    if rank == 0 and graph is not None:
+        try:
+            os.environ["B200_DEBUG_SKIP"] = "8"
+            s2 = torch.cuda.Stream()
+            s2.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s2):
+                step()
+                g2 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g2, stream=s2):
+                    step()
+            torch.cuda.current_stream().wait_stream(s2)
+            os.environ.pop("B200_DEBUG_SKIP", None)
+
+            def timed(gr, n):
+                for _ in range(3):
+                    gr.replay()
+                torch.cuda.synchronize()
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record()
+                for _ in range(n):
+                    gr.replay()
+                a1.record()
+                torch.cuda.synchronize()
+                return a0.elapsed_time(a1) * 1e-3 / n
+
+            n = max(10, a.steps)
+            t_full, t_skip = timed(graph, n), timed(g2, n)
+            wkv_in_step_s = max(t_full - t_skip, 0.0) / geom.n_layer
+            del g2
+        finally:
+            os.environ.pop("B200_DEBUG_SKIP", None)
+    ms, e2e_ms = dist_util.max_over_ranks([ms, e2e_s * 1e3], device=device)
     return dict(geom=geom, ms=ms, e2e_ms=e2e_ms, clocks=clk.summary(), launches=launches_per_step * a.steps,
-                graph=graph is not None, wkv_s=wkv_s, B=B)
+                graph=graph is not None, wkv_s=wkv_s, B=B, wkv_in_step_s=wkv_in_step_s)
+
+
+# ----------------------------------------------------------------------------------------------- engine / prefill / migration
+def engine_run(geom_name: str, n_workers: int, slots: int, requests_per_worker: int, max_tokens: int = 256, load_timeout_s: float = 900.0):
+    """BASELINE configs[2] as SURVEY §8(d) defines it: continuous batching through the AsyncEngineCore API — here
+    MPEngineCore: one worker PROCESS per GPU, one shared task queue — with `slots` decode slots per worker, synthetic prompts of
+    16-64 seeded tokens, max_tokens new tokens each, greedy, penalties 0, stop_tokens = [] (scripts/test_mmlu/test_mmlu.py:59-69).
+    Whole-job wall clock from the first submission to the last finish event, tokens counted where a client receives them."""
+    import asyncio
+
+    from chirrup_b200.engine import ModelLoadConfig
+    from chirrup_b200.engine_mp import MPEngineCore
+    from chirrup_b200.synth import GEOMETRIES
+
+    geom = GEOMETRIES[geom_name]
+
+    async def main():
+        eng = MPEngineCore()
+        t_load = time.perf_counter()
+        await eng.init(n_workers, ModelLoadConfig(vocab_size=geom.vocab_size, synthetic={"geom": geom_name, "seed": 0,
+                                                                                           "recipe": "trained_like"}),
+                       batch_size=slots, load_timeout_s=load_timeout_s, worker_options={"max_prefill_count": slots})
+        t_load = time.perf_counter() - t_load
+        g = torch.Generator().manual_seed(0)
+        kw = dict(top_k=1, presence_penalty=0.0, frequency_penalty=0.0, stop_tokens=[], max_tokens=max_tokens)
+
+        def make(n_req):
+            out = []
+            for _ in range(n_req):
+                n = int(torch.randint(16, 65, (1,), generator=g))
+                out.append(eng.completion(prefill_tokens=torch.randint(1, geom.vocab_size, (n,), generator=g).tolist(), **kw))
+            return out
+
+        async def drain(c):
+            return len(await c.get_full_completion())
+
+        # warm-up wave: step graphs captured, allocator settled, every worker's pipeline primed
+        warm = make(n_workers * slots)
+        await asyncio.gather(*[drain(c) for c in warm])
+        comps = make(n_workers * requests_per_worker)
+        t0 = time.perf_counter()
+        counts = await asyncio.gather(*[drain(c) for c in comps])
+        dt = time.perf_counter() - t0
+        eng.shutdown()
+        per_worker = {k: v["decode_tokens"] for k, v in eng.worker_steps.items()}
+        return sum(counts), dt, t_load, per_worker
+
+    n_tok, dt, t_load, per_worker = asyncio.run(main())
+    return {"value": n_tok / dt, "unit": "tok/s", "tokens": n_tok, "wall_s": dt, "workers": n_workers, "slots_per_worker": slots,
+            "requests": n_workers * requests_per_worker, "max_tokens": max_tokens, "load_s": t_load,
+            "decode_tokens_per_worker_incl_warmup": per_worker,
+            "api": "MPEngineCore.completion(prefill_tokens=...) async iteration: one worker process per GPU, one shared task "
+                   "queue, one event batch per worker step; prompts H2D at admission, sampled ids D2H every step"}
+
+
+def prefill_run(a, device):
+    """BASELINE configs[3]: 7.2B, 32 prompts x 4096 seeded tokens through prefill() in 512-token chunks (chunked tensor-core WKV,
+    persistent CTA-pair GEMMs), then the same with a shared 2048-token prefix served from the GPU-resident state cache."""
+    from chirrup_b200 import state_move
+    from chirrup_b200.state_cache import PrefixStateCache
+
+    geom, m = build_model(a.geom, device)
+    B, T, P, chunk = 32, 4096, 2048, 512
+    g = torch.Generator().manual_seed(0)
+    prefix = torch.randint(1, geom.vocab_size, (P,), generator=g)
+    prompts = torch.cat([prefix.expand(B, -1), torch.randint(1, geom.vocab_size, (B, T - P), generator=g)], 1).to(torch.int32)
+    host = prompts.pin_memory()
+
+    def timed(fn, n):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            r = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e-3 / n, r
+
+    st = m.generate_zero_state(B)
+    cold = lambda: m.prefill(host, st, chunk_len=chunk)          # host token ids in: the H2D copy is inside the timed region
+    for _ in range(max(1, min(a.warmup, 2))):
+        cold()
+    steps = max(1, min(a.steps, 5))
+    with ClockSampler(device.index or 0) as clk:
+        t_cold, lg_cold = timed(cold, steps)
+    os.environ["B200_WKV_SEQUENTIAL"] = "1"
+    try:
+        cold()
+        t_seq, _ = timed(cold, 1)
+    finally:
+        os.environ.pop("B200_WKV_SEQUENTIAL", None)
+    cache = PrefixStateCache(8)
+    s1 = m.generate_zero_state(1)
+    m.prefill(prompts[:1, :P], s1, chunk_len=chunk, want_logits=False)
+    cache.cache(tuple(prefix.tolist()), state_move.extract_slot(s1, 0))
+    st2 = m.generate_zero_state(B)
+
+    def warm():
+        for b in range(B):
+            rest, packed, n = cache.check(host[b].tolist())
+            assert n == P
+            state_move.inject_slot(st2, b, packed)
+        return m.prefill(host[:, P:], st2, chunk_len=chunk)
+
+    warm()
+    t_warm, lg_warm = timed(warm, 1)
+    flops = geom.gemm_flops_per_token() * B * T - 2 * geom.n_embd * geom.vocab_size * B * (T - 1)   # the head runs on B rows only
+    return dict(geom=geom, B=B, T=T, chunk=chunk, steps=steps, t_cold=t_cold, t_seq=t_seq, t_warm=t_warm, flops=flops,
+                clocks=clk.summary(), logits_rel=float((lg_warm.float() - lg_cold.float()).abs().max() / lg_cold.float().abs().max()))
 
 
 # ----------------------------------------------------------------------------------------------- main
@@ -412,12 +561,69 @@ def main():
         raise SystemExit("bench.py --impl ours needs a CUDA device: chirrup_b200 has no CPU path")
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    hbm_peak, tf_peak, which = peaks()
+    if a.config == "engine":
+        if rank != 0:
+            return
+        n = max(a.gpus, 1)
+        er = engine_run(a.geom, n, a.bsz, a.engine_requests)
+        out = dict(base)
+        out["config"] = dict(config, workload=f"RWKV-7 g1 {a.geom} continuous batching through the AsyncEngineCore worker loop, {a.bsz} "
+                             f"slots per worker, one worker process per GPU on one task queue, synthetic 16-64-token prompts, "
+                             f"256 new tokens, greedy (BASELINE.json configs[2] as SURVEY 8(d) defines it)")
+        out.update({"n_gpus": n, "value": er["value"], "ms_per_step": 1e3 * n * a.bsz / er["value"], "steps": er["tokens"] // (n * a.bsz),
+                    "e2e": dict(er, h2d_bytes_per_step=0, d2h_bytes_per_step=a.bsz * 4), "engine": er,
+                    "gpu_launches": (geom.n_layer * 8 + 6) * (er["tokens"] // a.bsz)})
+        print(json.dumps(out))
+        return
+    if a.config == "migration":
+        if rank != 0:
+            return
+        import subprocess
+
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "bench_migration.py")], capture_output=True, text=True)
+        line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        mig = json.loads(line[-1]) if line else {"unavailable": r.stderr[-500:]}
+        out = dict(base)
+        out["config"] = {"workload": "RWKV-7 g1 13.3B (L61, D4096) fp16 decode bsz 512/GPU with state-slot migration between two "
+                                     "workers over NVLink P2P (BASELINE.json configs[4])"}
+        if "unavailable" not in mig:
+            v = sum(mig["decode_under_migration_tok_per_s_per_gpu"])
+            out.update({"n_gpus": 2, "value": v, "ms_per_step": max(mig["decode_under_migration_ms_per_step"]),
+                        "e2e": {"value": v, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": None})
+        out["migration"] = mig
+        print(json.dumps(out))
+        return
+    if a.config == "prefill":
+        if rank != 0:
+            return
+        r = prefill_run(a, device)
+        g = r["geom"]
+        tok = r["B"] * r["T"]
+        out = dict(base)
+        out["metric"] = "RWKV-7 7.2B chunked prefill tok/s @bsz32 x 4096 tokens (BASELINE.json configs[3])"
+        out["config"] = dict(config, workload=f"RWKV-7 g1 {a.geom} prefill of {r['B']} x {r['T']}-token synthetic prompts in {r['chunk']}-token "
+                             f"chunks (chunked tensor-core WKV), then with a shared 2048-token prefix served from the GPU state cache "
+                             f"(BASELINE.json configs[3])", batch_per_gpu=r["B"])
+        out.update({"n_gpus": 1, "steps": r["steps"], "value": tok / r["t_cold"], "ms_per_step": 1e3 * r["t_cold"],
+                    "e2e": {"value": tok / r["t_cold"], "unit": "tok/s", "h2d_bytes_per_step": tok * 4, "d2h_bytes_per_step": 0,
+                            "api": "RWKV_x070.prefill(pinned host token ids, chunk_len=512)"},
+                    "clocks": r["clocks"],
+                    "prefill": {"cold_s": r["t_cold"], "sequential_wkv_kernel_s": r["t_seq"], "chunked_over_sequential": r["t_seq"] / r["t_cold"],
+                                "cache_hit_s": r["t_warm"], "cache_hit_speedup": r["t_cold"] / r["t_warm"],
+                                "logits_rel_cached_vs_cold": r["logits_rel"]},
+                    "roofline": {"bound": "tensor", "achieved": r["flops"] / r["t_cold"] / 1e12, "peak": tf_peak, "unit": "TFLOP/s",
+                                 "frac": r["flops"] / r["t_cold"] / 1e12 / tf_peak, "traffic": None, "peak_source": which,
+                                 "kernel": "whole prefill pass: GEMM flops of the step over its wall time (GEMMs + chunked WKV + glue)"},
+                    "gpu_launches": (g.n_layer * 8 + 4) * (r["T"] // r["chunk"]) * r["steps"]})
+        print(json.dumps(out))
+        return
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.distributed.init_process_group("nccl", device_id=device)
+        host_group = torch.distributed.new_group(backend="gloo")   # host-side waits (an NCCL barrier would spin on the GPUs)
     r = run_ours(a, rank, world, device)
     if rank == 0:
-        hbm_peak, tf_peak, which = peaks()
         n = max(world, 1)
         value = n * a.bsz * a.steps / (r["ms"] * 1e-3)
         e2e = n * a.bsz * a.steps / (r["e2e_ms"] * 1e-3)
@@ -439,7 +645,8 @@ def main():
         out.update({
             "value": value, "ms_per_step": r["ms"] / a.steps,
             "e2e": {"value": e2e, "unit": "tok/s", "h2d_bytes_per_step": a.bsz * 4, "d2h_bytes_per_step": a.bsz * 4,
-                    "api": "RWKV_x070.forward_seq_batch_seperate(host token ids) + greedy sample + D2H of the ids"},
+                    "api": "RWKV_x070.forward_seq_batch_seperate(List[List[int]] token ids, as chirrup/worker.py:690-704 passes "
+                           "them) + greedy sample + D2H of the ids, host-synchronised every step"},
             "gpu_launches": r["launches"], "cuda_graph": r["graph"], "clocks": r["clocks"],
             "roofline": {"bound": "hbm", "kernel": "wkv7_fused_one_kernel (T=1): kk-normalise + k,v mix + WKV-7 state update + GroupNorm + bonus + gate",
                          "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
@@ -449,10 +656,31 @@ def main():
                          "plain_wkv_kernel": {"achieved": achieved_plain, "frac": achieved_plain / hbm_peak,
                                               "algorithmic_bytes_per_launch": wkv_bytes,
                                               "us_per_launch": r["wkv_s"]["plain"] * 1e6}},
-            "gemm": {"flops_per_step": g.gemm_flops_per_token() * a.bsz,
-                     "achieved_tflops_if_rest_of_step": g.gemm_flops_per_token() * a.bsz / max(1e-9, (r["ms"] * 1e-3 / a.steps - r["wkv_s"]["fused"] * g.n_layer)) / 1e12,
-                     "peak_tflops": tf_peak},
         })
+        step_s = r["ms"] * 1e-3 / a.steps
+        wkv_in = r.get("wkv_in_step_s")
+        if wkv_in:
+            out["roofline"]["in_step"] = {
+                "us_per_launch": wkv_in * 1e6, "achieved": fused_bytes / wkv_in / 1e9, "frac": fused_bytes / wkv_in / 1e9 / hbm_peak,
+                "frac_of_8TBps_nominal": fused_bytes / wkv_in / 1e9 / 8000.0,
+                "how": "step graph minus the same graph with the 32 fused-WKV launches knocked out (upper bound on the kernel's "
+                       "in-step cost: the knock-out also breaks the programmatic-dependent-launch chain around it)"}
+        rest_s = step_s - (wkv_in or r["wkv_s"]["fused"]) * g.n_layer
+        gf = g.gemm_flops_per_token() * a.bsz
+        out["roofline_gemm"] = {"bound": "tensor", "achieved": gf / max(rest_s, 1e-9) / 1e12, "peak": tf_peak, "unit": "TFLOP/s",
+                                "frac": gf / max(rest_s, 1e-9) / 1e12 / tf_peak, "traffic": None, "peak_source": which + " (sustained bf16)",
+                                "flops_per_step": gf, "seconds": rest_s,
+                                "kernel": "GEMM phase = the step minus the in-step WKV time: tcgen05 CTA-pair GEMMs (r/k/v + LoRA group, "
+                                          "LoRA-up group, output projection, FFN key, FFN value, head) with the LayerNorm/shift/mix glue "
+                                          "between them counted against it"}
+        if not a.no_engine:
+            # the same configuration through the continuous-batching worker loop (what a Chirrup deployment runs): one worker
+            # process per GPU behind MPEngineCore, spawned by rank 0 on the GPUs the ranks just used (they are idle now)
+            try:
+                out["engine"] = engine_run(a.geom, n, a.bsz, a.engine_requests)
+                out["engine"]["fraction_of_bare_step"] = out["engine"]["value"] / value
+            except Exception as e:  # noqa: BLE001
+                out["engine"] = {"value": None, "error": repr(e)[:400]}
         if not a.skip_cpu_baseline and world == 1:
             try:
                 out["cpu_baseline"] = cpu_baseline_subprocess(a.geom, a.bsz)
@@ -461,7 +689,9 @@ def main():
                                        "sample": f"failed: {e!r}"[:400]}
         print(json.dumps(out))
     if world > 1:
-        torch.distributed.barrier()
+        del r
+        torch.cuda.empty_cache()
+        torch.distributed.barrier(group=host_group)      # ranks > 0 wait here (on the host) while rank 0 runs the engine phase
         torch.distributed.destroy_process_group()
 
 

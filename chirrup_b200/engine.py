@@ -21,6 +21,7 @@ from __future__ import annotations
 import asyncio
 import enum
 import queue
+from collections import deque
 import threading
 import time
 import uuid
@@ -101,6 +102,7 @@ class Task:                                                 # core_structure.py:
     cache_prefill: bool = False
     cache_prefill_padding: int = 0
     return_logits: bool = False
+    state_ready: Any = None                                 # optional CUDA event: `state` (device tensors) is complete after it
     output_queue: Any = None                                # thread-safe channel back to the asyncio side
     task_event_queue: "queue.Queue" = field(default_factory=queue.Queue)
     request_status: RequestStatus = field(init=False, default=RequestStatus.WAITING)
@@ -127,6 +129,8 @@ class ModelLoadConfig:                                      # core_structure.py:
     head_size: int = 64
     state_dict: Optional[Dict[str, torch.Tensor]] = None    # synthetic checkpoints (no .pth on disk)
     vocab_path: Optional[str] = None
+    synthetic: Optional[Dict[str, Any]] = None              # {"geom": "7.2B", "seed": 0, "recipe": "trained_like"}: each worker
+    #                                                         generates the seeded random-init checkpoint on its own GPU
 
 
 @dataclass
@@ -135,6 +139,8 @@ class _Slot:
     category: StateCategory = StateCategory.EMPTY
     pending: List[int] = field(default_factory=list)        # prompt tokens not yet consumed
     next_token: int = 0
+    prompt: Tuple[int, ...] = ()                            # the task's prompt as admitted (key material of cache_prefill)
+    prefill_cached: bool = False
 
 
 _MODEL_LOAD_LOCK = threading.Lock()                          # worker.py:82-83
@@ -176,6 +182,8 @@ class Worker:
         self._step_bufs = None
         self.pipeline = True
         self.sample_seed = 0x5EED0000 + sum(map(ord, str(worker_id)))
+        self.perf_queue: Optional["queue.Queue"] = None       # worker -> engine telemetry ("worker_performance", worker.py:858-884)
+        self._loop_times: "deque[float]" = deque(maxlen=10)   # worker.py:184
         self.no_penalty_token_ids = (33, 10, 49, 50, 51, 52, 53, 54, 55, 56, 57, 58)   # worker.py:173: "!", "\n", digits
         self._no_penalty_dev = None
         self._stop = False
@@ -193,7 +201,15 @@ class Worker:
 
             with _MODEL_LOAD_LOCK:                            # worker.py:209
                 args = make_args(self.model_config.model_path, self.model_config.vocab_size, self.model_config.head_size)
-                self.model = RWKV_x070(args, state_dict=self.model_config.state_dict, device=self.device)
+                sd = self.model_config.state_dict
+                if sd is None and self.model_config.synthetic:
+                    from .synth import GEOMETRIES, make_checkpoint
+
+                    syn = self.model_config.synthetic
+                    sd = make_checkpoint(GEOMETRIES[syn["geom"]], seed=syn.get("seed", 0), recipe=syn.get("recipe", "trained_like"),
+                                         device=self.device, dtype=torch.float16, n_layer=syn.get("n_layer"))
+                self.model = RWKV_x070(args, state_dict=sd, device=self.device)
+                del sd
         self.batch_state = self.model.generate_zero_state(self.batch_size)      # worker.py:260
         self._out_host = torch.empty((2, self.batch_size), dtype=torch.int32)    # double-buffered: one per step in flight
         if self.device.type == "cuda":
@@ -205,15 +221,49 @@ class Worker:
     def categories(self) -> List[StateCategory]:
         return [s.category for s in self.slots]
 
-    def _classify(self, slot: _Slot) -> None:
-        """DECODE / ONE_PREFILL / SEQ by remaining prompt length vs min_forward_seq_len (worker.py:646-654)."""
+    @staticmethod
+    def _keep(task: Task) -> int:
+        """Prompt tokens a sequence forward must leave unconsumed beyond the next input token: max(padding - 1, 0)
+        (worker.py:649, :746-750) — the state is wanted for caching at exactly that point."""
+        return max(int(task.cache_prefill_padding) - 1, 0)
+
+    def _classify(self, slot: _Slot, admission: bool = False) -> None:
+        """DECODE / ONE_PREFILL / SEQ by remaining prompt length vs min_forward_seq_len.  `pending` holds the next input token
+        plus what the reference calls task.prefill_tokens, so its `len(prefill_tokens)` is n - 1 here.  At admission the
+        padding term counts (worker.py:646-654); after a sequence forward it does not (worker.py:437-446), but the slot leaves
+        the SEQ group when only the padding is left (worker.py:411-420)."""
         n = len(slot.pending)
+        rem, keep = n - 1, self._keep(slot.task) if slot.task is not None else 0
         if n == 0:
             slot.category = StateCategory.FORWARD_ONE_DECODE
-        elif n > self.min_forward_seq_len:
-            slot.category = StateCategory.FORWARD_SEQ
-        else:
+        elif rem - keep <= 0 or (rem - keep if admission else rem) < self.min_forward_seq_len:
             slot.category = StateCategory.FORWARD_ONE_PREFILL
+        else:
+            slot.category = StateCategory.FORWARD_SEQ
+
+    def _maybe_cache_prefill(self, pos: int) -> None:
+        """("cache_prefill", {"state", "prefilled_tokens"}) when exactly max(padding - 1, 0) prompt tokens remain behind the next
+        input token (worker.py:411-435 after a sequence forward, :457-476 on the one-token path).  The reference copies the
+        slot to the host; here the copy stays on the GPU (`state_move.extract_slot`, stream-ordered behind the forward that
+        produced it) and carries a CUDA event under "ready" for consumers on other streams / devices."""
+        from . import state_move
+
+        s = self.slots[pos]
+        t = s.task
+        if t is None or not t.cache_prefill or s.prefill_cached or not s.pending:
+            return
+        if len(s.pending) - 1 != self._keep(t):
+            return
+        s.prefill_cached = True
+        key = s.prompt[:len(s.prompt) - len(s.pending)]
+        if not key or t.output_queue is None:
+            return
+        st = state_move.extract_slot(self.batch_state, pos)
+        ready = None
+        if self.device.type == "cuda":
+            ready = torch.cuda.Event()
+            ready.record()
+        t.output_queue.put_nowait(("cache_prefill", {"state": st, "prefilled_tokens": tuple(key), "ready": ready}))
 
     def _fill_task_pool(self) -> int:
         """Admit waiting tasks into EMPTY slots, at most max_prefill_count per loop (worker.py:570-669)."""
@@ -233,14 +283,17 @@ class Worker:
             if task.state is None:
                 state_move.clear_slot(self.batch_state, pos)                     # generate_zero_state(1), worker.py:586-589
             else:
+                ready = task.state_ready if task.state_ready is not None else getattr(task.state, "ready", None)
+                if ready is not None and self.device.type == "cuda":
+                    torch.cuda.current_stream().wait_event(ready)                # the cached copy may still be in flight
                 state_move.inject_slot(self.batch_state, pos, task.state)        # task.state[i].cuda(), worker.py:591-597
             self._set_slot_params(pos, task)
             if self._occ_host is not None:
                 self._occ_host[pos].zero_()
             toks = list(task.prefill_tokens) or [0]
-            slot.task, slot.pending = task, toks
+            slot.task, slot.pending, slot.prompt, slot.prefill_cached = task, toks, tuple(toks), False
             task.request_status = RequestStatus.RUNNING
-            self._classify(slot)
+            self._classify(slot, admission=True)
             admitted += 1
             budget -= 1
         return admitted
@@ -256,7 +309,9 @@ class Worker:
         seq = groups[StateCategory.FORWARD_SEQ]
         if not seq:
             return 0
-        T = min(self.max_forward_seq_len_per_forward, min(len(self.slots[p].pending) - 1 for p in seq))
+        T = min(self.max_forward_seq_len_per_forward,
+                min(len(self.slots[p].pending) - 1 - self._keep(self.slots[p].task) for p in seq))      # worker.py:746-754
+        assert T > 0
         toks = [self.slots[p].pending[:T] for p in seq]
         idx = torch.tensor(seq, dtype=torch.int32, device=self.device)
         st, el = self._state_for(idx)
@@ -266,6 +321,7 @@ class Worker:
             s = self.slots[p]
             del s.pending[:T]
             self._classify(s)
+            self._maybe_cache_prefill(p)
         self.steps["prefill"] += 1
         self.steps["prefill_tokens"] += T * len(seq)
         return T * len(seq)
@@ -389,6 +445,9 @@ class Worker:
         buffer — NO host synchronisation.  `feed` = the previous step's device-resident ids when they are exactly the input
         tokens of this step (every row decoding, same rows), else None: tokens come from the host-side slot table."""
         n = len(rows)
+        for p in rows:                                                           # worker.py:457-476
+            if self.slots[p].pending and self.slots[p].task.cache_prefill:
+                self._maybe_cache_prefill(p)
         if feed is None:
             toks = []
             for p in rows:
@@ -536,12 +595,36 @@ class Worker:
 
     def step(self) -> int:
         """One iteration of the main loop (worker.py:793-889): events, admission, decode step, periodic prefill chunk."""
+        t_loop = time.perf_counter()
         self._process_events()
         self._fill_task_pool()
+        layout = group_slots(self.categories()) if self.perf_queue is not None else None   # the batch layout this loop runs
         n = self._run_forward_one()
         if self.steps["decode"] % self.decode_prefill_ratio == 0 or n == 0:      # worker.py:854-856
             n += self._run_forward_seq()
+        if n:
+            self._loop_times.append(time.perf_counter() - t_loop)
+            if layout is not None:
+                self._emit_performance(*layout)
         return n
+
+    def _emit_performance(self, groups, offsets) -> None:
+        """(worker_id, "worker_performance", {...}) with the reference's payload keys (worker.py:858-884), consumed by
+        ``AsyncEngineCore.iter_worker_performance`` (engine_core.py:290-325).  Dropped when the consumer lags (bounded queue)."""
+        names = ("decode_offset", "one_prefill_offset", "decode_suspended_offset", "seq_perfill_offset", "accomplished_offset")
+        mem = torch.cuda.max_memory_allocated(self.device) / 1024 ** 3 if self.device.type == "cuda" else 0.0
+        info = (self.worker_id, "worker_performance", {
+            "avg_loop_time": sum(self._loop_times) / len(self._loop_times),
+            "state_size": self.batch_size,
+            "state_offset_details": dict(zip(names, offsets[:5])),
+            "task_details": {"decode_count": len(groups[StateCategory.FORWARD_ONE_DECODE]),
+                             "one_prefill_count": len(groups[StateCategory.FORWARD_ONE_PREFILL]),
+                             "seq_prefill_count": len(groups[StateCategory.FORWARD_SEQ])},
+            "max_allocated_memory_GB": mem})
+        try:
+            self.perf_queue.put_nowait(info)
+        except queue.Full:
+            pass
 
     def start(self) -> None:
         self._init_worker()
@@ -595,11 +678,68 @@ class AsyncEngineCompletion:
     async def get_full_completion(self) -> List[int]:
         toks = []
         async for ev in self:
-            toks.append(ev[1])
+            if ev[0] == "token":
+                toks.append(ev[1])
         return toks
 
     def abort(self) -> None:
         self.task.task_event_queue.put("abort")                                  # interface.py:140-142
+
+
+class CachedState(list):
+    """A cached single-request state ([(L,2,1,C), (L,1,H,64,64), (1,)] device tensors) with the CUDA event after which the
+    copy is complete; `Worker._fill_task_pool` waits on it before injecting (possibly on another GPU's stream)."""
+    ready: Any = None
+
+
+class CachedCompletion:
+    """What ``chirrup/web_service/app.py`` does around ``engine_core.completion`` when ``use_state_cache`` is set, as one
+    object (the HTTP layer itself is out of scope): ``check_and_wait_prefill`` before submitting (``app.py:187-190``), the
+    request runs from the cached state on the uncached remainder (``:202-214``), and the worker's ``("cache_prefill", ...)``
+    event feeds the cache and wakes identical requests parked on it (``:293-298``, ``:367-371``).  One deliberate deviation:
+    the new entry is keyed by the FULL consumed prompt (cached prefix + the tokens this request prefilled); the reference keys
+    it by the latter alone (``app.py:295-297``), which is a different string whenever the request itself started from a hit."""
+
+    def __init__(self, engine: "AsyncEngineCore", cache, prefill_tokens: Sequence[int], cache_prefill_padding: int = 0,
+                 use_state_cache: bool = True, cache_prefill: bool = True, **kw):
+        self.engine, self.cache, self.tokens = engine, cache, list(prefill_tokens)
+        self.padding, self.use_state_cache, self.cache_prefill, self.kw = cache_prefill_padding, use_state_cache, cache_prefill, kw
+        self.inner: Optional[AsyncEngineCompletion] = None
+        self.cached_token_len = 0
+
+    async def _submit(self):
+        rest, state, n = self.tokens, None, 0
+        if self.use_state_cache:
+            rest, state, n = await self.cache.check_and_wait_prefill(self.tokens, self.padding)
+        self.cached_token_len = n
+        self.inner = self.engine.completion(prefill_tokens=list(rest), state=state, cache_prefill=self.cache_prefill,
+                                            cache_prefill_padding=self.padding, **self.kw).start()
+
+    def __aiter__(self):
+        return self
+
+    async def __anext__(self):
+        if self.inner is None:
+            await self._submit()
+        while True:
+            ev = await self.inner.__anext__()
+            if ev[0] != "cache_prefill":
+                return ev
+            st = CachedState(ev[1]["state"])
+            st.ready = ev[1].get("ready")
+            key = self.cache.cache(tuple(self.tokens[:self.cached_token_len]) + tuple(ev[1]["prefilled_tokens"]), st)
+            await self.cache.awake_hang_up_prefills(key)
+
+    @property
+    def finish_reason(self):
+        return self.inner.finish_reason if self.inner is not None else None
+
+    async def get_full_completion(self) -> List[int]:
+        return [ev[1] async for ev in self if ev[0] == "token"]
+
+    def abort(self) -> None:
+        if self.inner is not None:
+            self.inner.abort()
 
 
 class AsyncEngineCore:
@@ -614,6 +754,19 @@ class AsyncEngineCore:
         self.is_shutdown = False
         self.tokenizer = IdTokenizer()
         self.event_loop: Optional[asyncio.AbstractEventLoop] = None
+        self.perf_queue: "queue.Queue" = queue.Queue(maxsize=800)
+
+    async def iter_worker_performance(self, timeout: float = 1.0):
+        """engine_core.py:290-325: async generator over the workers' ("worker_performance") telemetry, as dicts with the
+        reference's WorkerPerformanceInfo fields."""
+        while not self.is_shutdown:
+            try:
+                worker_id, kind, payload = self.perf_queue.get_nowait()
+            except queue.Empty:
+                await asyncio.sleep(min(timeout, 0.05))
+                continue
+            if kind == "worker_performance":
+                yield dict(worker_id=worker_id, **payload)
 
     def init(self, worker_num: int, model_config: ModelLoadConfig, batch_size: int = 32, tokenizer=None,
              load_timeout_s: float = 300.0) -> "asyncio.Task":
@@ -623,6 +776,7 @@ class AsyncEngineCore:
         for k in range(worker_num):                                              # engine_core.py:135-153
             w = Worker(f"worker_{k}", [k], model_config, self.task_queue, self.master_event_queue, batch_size=batch_size,
                        tokenizer=self.tokenizer)
+            w.perf_queue = self.perf_queue
             th = threading.Thread(target=w.start, daemon=True, name=w.worker_id)
             self.workers.append(w)
             self.threads.append(th)

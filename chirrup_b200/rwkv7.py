@@ -64,6 +64,8 @@ class RWKV_x070:
         self._graphs: "OrderedDict[tuple, torch.cuda.CUDAGraph]" = OrderedDict()
         self._graph_seen: Dict[tuple, int] = {}
         self._capture_stream = None
+        self._gio = None
+        self.graph_hits = self.graph_misses = 0
         raw = state_dict if state_dict is not None else torch.load(args.MODEL_NAME + ".pth", map_location="cpu")
         self.n_head, self.head_size = raw["blocks.0.att.r_k"].shape          # rwkv7.py:173
         assert self.head_size == HEAD_SIZE
@@ -126,10 +128,26 @@ class RWKV_x070:
         if self._ws is None or n_tokens > self._ws_tokens:
             cap = max(n_tokens, 64)
             need = _lib.lib().b200_model_workspace_bytes(self._handle, cap)
+            # captured step graphs hold the OLD workspace address: they die with it
+            self._graphs.clear()
+            self._graph_seen.clear()
             self._ws = None
             self._ws = torch.zeros((need,), dtype=torch.uint8, device=self.device)
             self._ws_tokens = cap
         return self._ws
+
+    def _graph_io(self, B: int):
+        """Model-owned staging buffers of the graphed decode step (token ids, slot indices, logits): a captured graph then
+        depends on the caller's STATE tensors only, not on where this call's token / slot-index / logits tensors happen to
+        live (a fresh ``torch.tensor(list)`` every step, a new index tensor whenever rows join or leave the batch)."""
+        if self._gio is None or self._gio[0].numel() < B:
+            cap = max(B, 64)
+            self._graphs.clear()
+            self._graph_seen.clear()
+            self._gio = (torch.zeros((cap,), dtype=torch.int32, device=self.device),
+                         torch.zeros((cap,), dtype=torch.int32, device=self.device),
+                         torch.empty((cap, self.vocab_size), dtype=DTYPE, device=self.device))
+        return self._gio
 
     # ---------------------------------------------------------------- state
     def generate_zero_state(self, bsz: int) -> List[torch.Tensor]:
@@ -164,33 +182,52 @@ class RWKV_x070:
             sp = slot_idx.data_ptr()
         elif n_slots < B:
             raise ValueError("state has fewer rows than sequences")
-        logits = None
-        if want_logits:
+        graphed = T == 1 and self.graph_decode and not torch.cuda.is_current_stream_capturing()
+        ws = self._workspace(B * T)
+        logits, staged = None, None
+        tok_ptr = tokens.data_ptr()
+        if graphed:
+            # stage the per-call operands in model-owned buffers so that the graph key is (B, state tensors, switches) only
+            tok_buf, slot_buf, lg_buf = self._graph_io(B)
+            tok_buf[:B].copy_(tokens.view(-1), non_blocking=True)
+            tok_ptr = tok_buf.data_ptr()
+            if slot_idx is not None:
+                slot_buf[:B].copy_(slot_idx, non_blocking=True)
+                sp = slot_buf.data_ptr()
+            if want_logits:
+                if out is not None:
+                    logits = out                       # a caller-owned fixed buffer (the worker's): part of the key
+                else:
+                    logits = staged = lg_buf[:B]
+        elif want_logits:
             rows = B * T if full_output else B
             logits = out if out is not None else torch.empty((rows, V), dtype=DTYPE, device=self.device)
-        ws = self._workspace(B * T)
-        cargs = (self._handle, B, T, tokens.data_ptr(), s0.data_ptr(), s0.stride(0), s0.stride(1), s1.data_ptr(), s1.stride(0),
+        cargs = (self._handle, B, T, tok_ptr, s0.data_ptr(), s0.stride(0), s0.stride(1), s1.data_ptr(), s1.stride(0),
                  n_slots, s2.data_ptr(), sp, logits.data_ptr() if logits is not None else 0, 1 if full_output else 0,
                  ws.data_ptr(), ws.numel())
 
         def launch():
             _lib.check(_lib.lib().b200_model_forward(*cargs, _stream(self.device)), "b200_model_forward")
 
-        if T == 1 and self.graph_decode and not torch.cuda.is_current_stream_capturing():
+        if graphed:
             # the A/B switches model.cu reads per call are part of what a captured graph froze
             self._step_graphed(cargs[1:] + tuple(os.environ.get(k) for k in _STEP_ENV), launch)
         else:
             launch()
         if logits is None:
             return None
+        if staged is not None:
+            logits = staged.clone()                    # the reference returns a fresh tensor every call
         return logits.view(B, T, V) if full_output else logits
 
     def _step_graphed(self, key: tuple, launch) -> None:
         g = self._graphs.get(key)
         if g is not None:
             self._graphs.move_to_end(key)
+            self.graph_hits += 1
             g.replay()
             return
+        self.graph_misses += 1
         seen = self._graph_seen.get(key, 0) + 1
         if seen < self.graph_after:
             if len(self._graph_seen) > 256:

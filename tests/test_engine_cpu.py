@@ -45,33 +45,7 @@ def test_grouping_is_the_sort_without_moving_rows():
             assert b - a == cats.count(c)
 
 
-class ToyModel:
-    """CPU stand-in with the model's calling convention: next token = (last input + 1) mod V, elapsed += T; records every call."""
-
-    def __init__(self, V=50, L=2, C=8):
-        self.device = torch.device("cpu")
-        self.V, self.L, self.C = V, L, C
-        self.vocab_size = V
-        self.calls = []
-
-    def generate_zero_state(self, bsz):
-        return [torch.zeros((self.L, 2, bsz, self.C), dtype=torch.float16), torch.zeros((self.L, bsz, 1, 64, 64), dtype=torch.float16),
-                torch.zeros((bsz,), dtype=torch.int32)]
-
-    def _tokens(self, idxs):
-        return torch.tensor(idxs, dtype=torch.int32).reshape(-1)
-
-    def _step(self, tokens, B, T, state, full_output, want_logits=True, slot_idx=None, out=None):
-        self.calls.append((B, T, slot_idx.tolist() if slot_idx is not None else None))
-        tk = tokens.view(B, T).long()
-        state[2] += T
-        rows = slot_idx.long()
-        state[0][0, 0, rows, 0] += tk.sum(1).to(torch.float16)          # a visible trace of what each slot consumed
-        if not want_logits:
-            return None
-        lg = torch.zeros((B, self.V), dtype=torch.float16)
-        lg[torch.arange(B), (tk[:, -1] + 1) % self.V] = 5.0
-        return lg
+from toy_model import ToyModel  # noqa: E402  (CPU stand-in with the model's calling convention)
 
 
 def make_worker(bsz=8, V=50):
@@ -190,3 +164,96 @@ def test_stop_token_is_neither_recorded_nor_streamed():
 def test_greedy_classification_follows_the_reference_worker():
     assert Task(top_k=1).is_greedy() and Task(top_p=0.0).is_greedy()
     assert not Task(temperature=0.0).is_greedy()          # worker.py:611-613: temperature <= 0 becomes 1.0 and still samples
+
+
+def _run_until_idle(w, n=400):
+    for _ in range(n):
+        w.step()
+        if not w.busy() and w.task_queue.empty():
+            return
+    raise AssertionError("worker did not drain")
+
+
+@pytest.mark.parametrize("plen,pad", [(40, 0), (40, 3), (7, 2), (131, 7), (12, 1), (3, 0)])
+def test_cache_prefill_event_fires_at_the_reference_trigger_point(plen, pad):
+    """chirrup/worker.py:411-435, :457-476: exactly one ("cache_prefill", ...) event, carrying the slot state after
+    prompt[:len - max(padding, 1)] and that token tuple; sequence forwards never run into the padding (worker.py:746-754)."""
+    w = make_worker(bsz=4)
+    s = Sink()
+    prompt = [(7 * i) % 40 + 1 for i in range(plen)]
+    w.task_queue.put(Task(prefill_tokens=list(prompt), output_queue=s, top_k=1, max_tokens=2, stop_tokens=[],
+                          cache_prefill=True, cache_prefill_padding=pad))
+    _run_until_idle(w)
+    evs = [e for e in s.items if e[0] == "cache_prefill"]
+    n_key = plen - max(pad, 1)
+    if n_key <= 0:
+        assert not evs
+        return
+    assert len(evs) == 1
+    payload = evs[0][1]
+    assert payload["prefilled_tokens"] == tuple(prompt[:n_key])
+    # the ToyModel leaves a trace of what the slot consumed: elapsed == tokens consumed, state0[0,0,.,0] == their sum
+    assert int(payload["state"][2][0]) == n_key
+    assert float(payload["state"][0][0, 0, 0, 0]) == float(sum(prompt[:n_key]))
+    toks = [e[1] for e in s.items if e[0] == "token"]
+    assert toks == [(prompt[-1] + 1) % 50, (prompt[-1] + 2) % 50]          # the request itself is unaffected
+
+
+def test_cached_completion_prefix_hit_and_dedup_through_the_engine():
+    """app.py:187-214, :293-298 at the engine level: request 1 prefills and caches; an identical concurrent request waits and is
+    then served from the cache; a later request sharing the prefix starts from the cached state — all produce the tokens of a
+    cold run, and the worker consumed only the uncached remainder."""
+    from chirrup_b200.engine import CachedCompletion
+    from chirrup_b200.state_cache import PrefixStateCache
+
+    async def main():
+        eng = AsyncEngineCore()
+        eng.event_loop = asyncio.get_event_loop()
+        model = ToyModel()
+        w = Worker("w0", [0], ModelLoadConfig(), eng.task_queue, eng.master_event_queue, batch_size=4, model=model)
+        import threading
+
+        th = threading.Thread(target=w.start, daemon=True)
+        eng.workers.append(w)
+        eng.threads.append(th)
+        th.start()
+        eng.is_initialized = True
+        cache = PrefixStateCache(8)
+        prompt = [(3 * i) % 40 + 1 for i in range(30)]
+        kw = dict(top_k=1, max_tokens=3, stop_tokens=[])
+        a = CachedCompletion(eng, cache, prompt, cache_prefill_padding=2, **kw)
+        b = CachedCompletion(eng, cache, prompt, cache_prefill_padding=2, **kw)       # identical, concurrent: must wait for a
+        ta, tb = await asyncio.gather(a.get_full_completion(), b.get_full_completion())
+        assert ta == tb == [(prompt[-1] + 1 + i) % 50 for i in range(3)]
+        assert a.cached_token_len == 0 and b.cached_token_len == len(prompt) - 2
+        assert tuple(prompt[:-2]) in cache
+        c = CachedCompletion(eng, cache, prompt + [9, 9, 9, 9], cache_prefill_padding=2, **kw)   # shares the cached prefix
+        tc = await c.get_full_completion()
+        assert tc == [(9 + 1 + i) % 50 for i in range(3)] and c.cached_token_len == len(prompt) - 2
+        assert tuple((prompt + [9, 9, 9, 9])[:-2]) in cache                            # keyed by the FULL consumed prompt
+        eng.shutdown()
+        return model.calls
+
+    calls = asyncio.run(main())
+    consumed = sum(B * T for B, T, _ in calls)
+    # cold: 30 prompt tokens + 2 decode steps after the first sampled token; b: 2 + 2; c: 6 + 2  (vs 30 + 34 + ... uncached)
+    assert consumed <= (30 + 2) + (2 + 2) + (6 + 2) + 6
+
+
+def test_worker_performance_telemetry():
+    """chirrup/worker.py:858-884 -> engine_core.py:290-325: one ("worker_performance") record per busy loop with the
+    reference's payload keys."""
+    w = make_worker(bsz=8)
+    w.perf_queue = queue.Queue(maxsize=100)
+    w.task_queue.put(Task(prefill_tokens=list(range(1, 30)), output_queue=Sink(), top_k=1, max_tokens=3, stop_tokens=[]))
+    w.task_queue.put(Task(prefill_tokens=[4], output_queue=Sink(), top_k=1, max_tokens=3, stop_tokens=[]))
+    _run_until_idle(w)
+    recs = []
+    while not w.perf_queue.empty():
+        recs.append(w.perf_queue.get_nowait())
+    assert recs and all(r[0] == "w0" and r[1] == "worker_performance" for r in recs)
+    p = recs[0][2]
+    assert set(p) == {"avg_loop_time", "state_size", "state_offset_details", "task_details", "max_allocated_memory_GB"}
+    assert set(p["task_details"]) == {"decode_count", "one_prefill_count", "seq_prefill_count"} and p["state_size"] == 8
+    assert p["state_offset_details"]["decode_offset"][0] == 0 and p["avg_loop_time"] > 0
+    assert any(r[2]["task_details"]["seq_prefill_count"] == 1 for r in recs)

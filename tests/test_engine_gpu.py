@@ -227,3 +227,44 @@ def test_worker_sampled_requests_are_reproducible_and_respect_top_k():
             assert t in torch.topk(lg.float()[0], 3).indices.tolist()
             lg = m.forward_seq_batch([[t]], st)
     assert len({tuple(x) for x in a}) > 1
+
+
+def test_state_cache_hit_inside_the_engine_matches_cold_run():
+    """SURVEY §8(f)-3 through the engine (chirrup/web_service/app.py:187-214, :293-298; chirrup/worker.py:411-435, :457-476):
+    request 1 prefills a 180-token prompt and the worker emits its ("cache_prefill") state — kept on the GPU; an identical
+    concurrent request waits for it; request 3 shares the prefix and extends it.  Every request produces exactly the tokens of
+    a cold isolated run, and the cached requests consume only their uncached remainder."""
+    from chirrup_b200.engine import AsyncEngineCore, CachedCompletion, ModelLoadConfig
+    from chirrup_b200.state_cache import PrefixStateCache
+
+    geom = GEOMETRIES["small"]
+    raw = make_checkpoint(geom, seed=8, recipe="trained_like")
+    _, m_ref = _model()                                       # same seed: the isolated reference runs
+    g = torch.Generator().manual_seed(3)
+    prompt = torch.randint(1, geom.vocab_size, (180,), generator=g).tolist()
+    ext = prompt + torch.randint(1, geom.vocab_size, (25,), generator=g).tolist()
+    pad = 3
+
+    async def main():
+        eng = AsyncEngineCore()
+        await eng.init(worker_num=1, model_config=ModelLoadConfig(state_dict=raw, vocab_size=geom.vocab_size), batch_size=8)
+        cache = PrefixStateCache(8)
+        kw = dict(top_k=1, max_tokens=10, stop_tokens=[], presence_penalty=0.0, frequency_penalty=0.0)
+        a = CachedCompletion(eng, cache, prompt, cache_prefill_padding=pad, **kw)
+        b = CachedCompletion(eng, cache, prompt, cache_prefill_padding=pad, **kw)
+        ta, tb = await asyncio.gather(a.get_full_completion(), b.get_full_completion())
+        c = CachedCompletion(eng, cache, ext, cache_prefill_padding=pad, **kw)
+        tc = await c.get_full_completion()
+        w = eng.workers[0]
+        stats = dict(w.steps)
+        entry = cache.entries[tuple(prompt[:-pad])]
+        eng.shutdown()
+        return ta, tb, tc, (a.cached_token_len, b.cached_token_len, c.cached_token_len), stats, entry
+
+    ta, tb, tc, hits, stats, entry = asyncio.run(main())
+    assert hits == (0, len(prompt) - pad, len(prompt) - pad)
+    assert ta == tb == _greedy_alone(m_ref, prompt, 10)
+    assert tc == _greedy_alone(m_ref, ext, 10)
+    assert entry[0].is_cuda and int(entry[2][0]) == len(prompt) - pad          # GPU-resident tier; elapsed = tokens consumed
+    # prefill work: 180 (cold) + 3 (b: padding only) + 28 (c: padding + extension), none of the cached 177 tokens twice
+    assert stats["prefill_tokens"] <= 180 + 3 + 28

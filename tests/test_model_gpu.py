@@ -256,7 +256,10 @@ def test_chunked_prefill_and_state_cache_reuse():
     la = m.forward_seq_batch(toks.tolist(), sa)
     lb = m.prefill(toks, sb, chunk_len=7)
     assert torch.equal(sa[2], sb[2]) and int(sa[2][0]) == T
-    assert rel(lb, la) <= LOGIT_TOL and rel_l2(sb[1], sa[1]) <= STATE_TOL and rel_l2(sb[0], sa[0]) <= STATE_TOL
+    # T = 50 in one call runs the chunked tensor-core WKV kernel, 7-token calls the sequential one (bit-identical to the
+    # reference kernel): the two differ by the reference arithmetic's own per-token fp16 rounding, ~1e-3 on the state
+    # (tests/test_wkv_chunk_gpu.py, tools/wkv_chunk_emulate.py)
+    assert rel(lb, la) <= LOGIT_TOL and rel_l2(sb[1], sa[1]) <= 2 * STATE_TOL and rel_l2(sb[0], sa[0]) <= 2 * STATE_TOL
     cache = StateCache(max_gpu_entries=4)
     s1 = m.generate_zero_state(1)
     m.prefill(toks[:1, :P], s1, want_logits=False)
@@ -268,7 +271,7 @@ def test_chunked_prefill_and_state_cache_reuse():
         state_move.inject_slot(sc, b, packed)
     lc = m.prefill(toks[:, P:], sc)
     assert torch.equal(sc[2], sa[2])
-    assert rel(lc, la) <= LOGIT_TOL and rel_l2(sc[1], sa[1]) <= STATE_TOL
+    assert rel(lc, la) <= LOGIT_TOL and rel_l2(sc[1], sa[1]) <= 2 * STATE_TOL
 
 
 def test_fused_tmix_core_equals_three_kernel_chain():
@@ -414,3 +417,45 @@ def test_chained_ffn_launch_is_bit_identical_to_two_launches():
         assert torch.equal(a, b)
     assert torch.equal(sa[0], sb[0]) and torch.equal(sa[1], sb[1]) and torch.equal(sa[2], sb[2])
     assert torch.isfinite(ha[-1].float()).all()
+
+
+def test_step_graph_cache_is_keyed_on_state_not_on_call_tensors_and_survives_workspace_regrowth():
+    """The graphed decode step stages token ids / slot indices / logits in model-owned buffers: a fresh ``torch.tensor(list)``
+    per call (the worker's calling convention, chirrup/worker.py:690-704) or a new slot-index tensor when rows are re-ordered
+    still replays the same graph; when the activation workspace is re-allocated for a larger call the captured graphs (which
+    froze the old address) are dropped, never replayed.  Every step is compared bit for bit with an un-graphed twin."""
+    geom, raw, m = build("small", seed=4, recipe="trained_like")
+    _, _, twin = build("small", seed=4, recipe="trained_like")
+    twin.graph_decode = False
+    m.graph_after = 2
+    B, V = 4, geom.vocab_size
+    g = torch.Generator().manual_seed(6)
+    sa, sb = m.generate_zero_state(B + 2), twin.generate_zero_state(B + 2)
+    ea, eb = torch.zeros(B, dtype=torch.int32, device="cuda"), torch.zeros(B, dtype=torch.int32, device="cuda")
+
+    def both(tok_list, order):
+        idx_a = torch.tensor(order, dtype=torch.int32, device="cuda")          # a NEW index tensor every call
+        idx_b = torch.tensor(order, dtype=torch.int32, device="cuda")
+        la = m._step(m._tokens(tok_list), B, 1, [sa[0], sa[1], ea], False, slot_idx=idx_a)
+        lb = twin._step(twin._tokens(tok_list), B, 1, [sb[0], sb[1], eb], False, slot_idx=idx_b)
+        assert torch.equal(la, lb) and torch.equal(sa[1], sb[1]) and torch.equal(sa[0], sb[0]) and torch.equal(ea, eb)
+        return la
+
+    orders = [[0, 1, 2, 3], [3, 1, 5, 0], [2, 4, 0, 1]]
+    keep = None
+    for i in range(9):
+        toks = torch.randint(1, V, (B, 1), generator=g).tolist()
+        lg = both(toks, orders[i % 3])
+        if i == 5:
+            keep = lg.clone()
+            keep_ref = lg
+    assert torch.equal(keep, keep_ref), "a returned logits tensor was overwritten by a later step"
+    assert len(m._graphs) == 1 and m.graph_hits >= 6                            # one graph served every row order
+    # a larger call re-allocates the workspace: graphs captured against the old one must go
+    big = torch.randint(1, V, (B, 40), generator=g).tolist()
+    l1 = m._step(m._tokens(big), B, 40, [sa[0], sa[1], ea], False, slot_idx=torch.tensor(orders[0], dtype=torch.int32, device="cuda"))
+    l2 = twin._step(twin._tokens(big), B, 40, [sb[0], sb[1], eb], False, slot_idx=torch.tensor(orders[0], dtype=torch.int32, device="cuda"))
+    assert torch.equal(l1, l2) and len(m._graphs) == 0
+    for i in range(5):
+        both(torch.randint(1, V, (B, 1), generator=g).tolist(), orders[i % 3])
+    assert len(m._graphs) == 1
