@@ -34,6 +34,7 @@ SIGNATURES: Dict[str, tuple] = {
     "b200_layer_norm_f16": (_I, [_I, _I, _P, _P, _P, _P, _P]),
     "b200_model_create": (_I, [_I, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "b200_model_destroy": (None, [_P]),
+    "b200_model_set_ffn_value_rows": (_I, [_P, _P]),
     "b200_model_workspace_bytes": (_L, [_P, _I]),
     "b200_model_forward": (_I, [_P, _I, _I, _P, _P, _L, _L, _P, _L, _I, _P, _P, _P, _I, _P, _L, _P]),
     "b200_model_last_launch_count": (_I, [_P]),

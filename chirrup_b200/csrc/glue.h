@@ -60,6 +60,10 @@ int launch_wkv7_seq(int B, int T, int C, int H, void* state, long state_slot_str
                     const void* k, const void* v, const void* a, const void* b, void* y, const int* elapsed_t,
                     const int* slot_idx, cudaStream_t stream, bool pdl = false);
 
+// spmv.cu: out[c] = (res ? res[c] + : ) sum_{d : vec[d] != 0} vec[d] * mat[d*C + c]   (bsz-1 FFN value product, rwkv7.py:659)
+int launch_spmv(int D, int C, const __half* vec, const __half* mat, const __half* res, __half* out, cudaStream_t stream,
+                bool pdl = false);
+
 // gemm.cu
 int linear_f16_launch(int M, int N, int K, const void* A, long lda, const void* W, long ldw, void* out, long ldo,
                       const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,

@@ -13,6 +13,7 @@ struct b200_model {
     int L, C, V, H, F, d_w, d_a, d_v, d_g;
     const __half* gw[4];
     const __half** lw;  // L * B200_LW_COUNT
+    const __half** ffn_vt;  // optional: L pointers to ffn.value.weight in the reference's (F, C) layout (bsz-1 sparse product)
     int last_launches;
 };
 
@@ -75,14 +76,27 @@ extern "C" int b200_model_create(int n_layer, int n_embd, int vocab_size, int d_
     for (int i = 0; i < 4; i++) m->gw[i] = static_cast<const __half*>(global_w[i]);
     m->lw = new (std::nothrow) const __half*[(size_t)n_layer * B200_LW_COUNT];
     for (long i = 0; i < (long)n_layer * B200_LW_COUNT; i++) m->lw[i] = static_cast<const __half*>(layer_w[i]);
+    m->ffn_vt = nullptr;
     m->last_launches = 0;
     *out = m;
+    return 0;
+}
+
+extern "C" int b200_model_set_ffn_value_rows(b200_model* m, const void* const* ffn_value_fc) {
+    if (!m) return B200_ERR_BAD_ARG;
+    delete[] m->ffn_vt;
+    m->ffn_vt = nullptr;
+    if (!ffn_value_fc) return 0;
+    m->ffn_vt = new (std::nothrow) const __half*[(size_t)m->L];
+    if (!m->ffn_vt) return B200_ERR_BAD_ARG;
+    for (int i = 0; i < m->L; i++) m->ffn_vt[i] = static_cast<const __half*>(ffn_value_fc[i]);
     return 0;
 }
 
 extern "C" void b200_model_destroy(b200_model* m) {
     if (!m) return;
     delete[] m->lw;
+    delete[] m->ffn_vt;
     delete m;
 }
 
@@ -112,6 +126,7 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
     // enqueued before it); every kernel of the step calls griddepcontrol.wait before touching its predecessors' outputs.
     const bool pdl = getenv("B200_NO_PDL") == nullptr;
     const bool wkv_sequential = getenv("B200_WKV_SEQUENTIAL") != nullptr;
+    const bool no_spmv = getenv("B200_NO_SPMV") != nullptr;  // A/B switch: dense FFN value product at B = T = 1
     const bool no_group = getenv("B200_NO_PAIR") != nullptr;  // A/B switch: the one-CTA-per-tile GEMM path of gemm.cu
 #define RUN(call)                                                                                     \
     do {                                                                                              \
@@ -242,7 +257,12 @@ extern "C" int b200_model_forward(b200_model* m, int B, int T, const int* tokens
             }
             if (rc != 0 && rc != B200_ERR_UNSUPPORTED) return rc;
         }
-        if (!chained) {
+        if (M == 1 && m->ffn_vt && !no_spmv) {
+            // bsz-1 path (RWKV_x070_CMix_one, rwkv7.py:653-662): the ReLU^2 output is sparse, so the value product reads only
+            // the rows of the (F, C) matrix whose key activation is non-zero — rwkv_mm_sparsity / SPMV_OP, with the residual add
+            RUN_T(64, lin(M, F, C, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, nullptr, nullptr, B200_EPI_RELU_SQ));
+            RUN_T(128, launch_spmv(F, C, ws.hidden, m->ffn_vt[l], ws.x, ws.x, st, pdl));
+        } else if (!chained) {
             RUN_T(64, lin(M, F, C, ws.kx, w[B200_LW_FFN_KEY], ws.hidden, nullptr, nullptr, B200_EPI_RELU_SQ));
             // the last layer's x goes to ln_out, which takes finished rows
             RUN_T(128, lin(M, C, F, ws.hidden, w[B200_LW_FFN_VALUE], ws.x, nullptr, ws.x, B200_EPI_RESADD,

@@ -65,8 +65,12 @@ DEVI uint32_t pack2(float lo, float hi) {
     return *reinterpret_cast<uint32_t*>(&h);
 }
 DEVI uint32_t lds32(const __half* p) { return *reinterpret_cast<const uint32_t*>(p); }
-DEVI uint32_t pack_u16(const __half* lo, const __half* hi) {
-    return (uint32_t)(*reinterpret_cast<const unsigned short*>(lo)) | ((uint32_t)(*reinterpret_cast<const unsigned short*>(hi)) << 16);
+// four 8x8 b16 matrices, TRANSPOSED on the way in: lane l supplies the address of row (l & 7) of matrix (l >> 3); thread
+// (g, tq) receives elements (row 2tq, 2tq+1; column g) of each — the mma fragment of an operand stored k-major
+DEVI void ldmatrix_x4_trans(uint32_t (&r)[4], const __half* row_ptr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(smem_u32(row_ptr)));
 }
 
 // D = A (16x16, row) * B (16x8, col) + D, fp16 operands, fp32 accumulate
@@ -83,14 +87,13 @@ struct ChunkSmem {
     float em[HS], ecTm[HS];                    // 2^m, 2^(c_16 - m) per channel
     alignas(16) __half opT[2 * TC][LDO];       // rows 0..15 a~_t, rows 16..31 r~_t           [t][j]
     alignas(16) __half opS[2 * TC][LDO];       // rows 0..15 b~_s, rows 16..31 k~_s           [s][j]
-    alignas(16) __half vT[HS][LDS16];          // v' transposed                               [i][s]
     alignas(16) __half aakT[TC][LDS16];        // Aak, Abr, Akr, (I - Aab)^-1 as B operands   [t][s]
     alignas(16) __half abrT[TC][LDS16];
     alignas(16) __half akrT[TC][LDS16];
     alignas(16) __half tinvT[TC][LDS16];
     float aab[TC][TC + 1];                     // Aab in fp32 for the triangular inverse      [s][t]
     float ys[TC][LDY];                         // y of the chunk                               [t][i]
-    alignas(16) __half v2s[TC][HS];            // v' and gate per token for the output stage   [t][i]
+    alignas(16) __half v2s[TC][LDO];           // v' per token: A operand (via ldmatrix.trans) and output stage   [s][i]
     alignas(16) __half gs[TC][HS];
     float bonus[TC];
     alignas(8) uint64_t bar;
@@ -123,13 +126,6 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
     // prep mapping: thread -> (token tk of the chunk, 8 consecutive channels)
     const int tk = tid >> 3, cg = tid & 7;
     const int ch0 = h * HS + cg * 8;
-    // per-channel weights are re-read (L1-resident) where they are used instead of living in 40 registers next to the state
-    auto ldw8 = [&](const __half* base, float (&out)[8]) {
-        const int4 q = *reinterpret_cast<const int4*>(base + ch0);
-        const __half* hh = reinterpret_cast<const __half*>(&q);
-#pragma unroll
-        for (int e = 0; e < 8; e++) out[e] = __half2float(hh[e]);
-    };
     pdl_wait();  // the state tile and the per-channel weights do not depend on the preceding kernels; r..g below do
 
     // ---- the state: fp32 accumulator fragments for the whole launch.  Warp w owns rows 16w..16w+15; S[n][0..3] = rows
@@ -149,57 +145,67 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
 
     for (int t0 = 0; t0 < T; t0 += TC) {
         // ================================================================ 1. vector prep of 16 tokens (rwkv7.py:632-637)
+        // Every reference op here acts on fp16 tensors (fp32 inside the op, one rounding): exactly one correctly rounded
+        // half op (sums and products of two binary16 values are exact in fp32), so the prep runs on half2 pairs.
         const int t = t0 + tk;
         const bool live = t < T;
-        float a_vec[8], b_vec[8], k2[8], rr[8], ld[8];
+        __half2 a_vec[4], b_vec[4], k2[4], rr[4];
+        float ld[8];
         {
-            float kin[8], vin[8], ain[8], win[8], gin[8], vg[8], vf[8], kk_w[8], ka_w[8], rk_w[8];
-            ldw8(p.k_k, kk_w); ldw8(p.k_a, ka_w); ldw8(p.r_k, rk_w);
             const size_t idx = ((size_t)bb * T + (live ? t : 0)) * C + ch0;
-            auto ld8 = [&](const __half* base, float (&out)[8]) {
-                const int4 q = *reinterpret_cast<const int4*>(base + idx);
-                const __half* hh = reinterpret_cast<const __half*>(&q);
-#pragma unroll
-                for (int e = 0; e < 8; e++) out[e] = __half2float(hh[e]);
-            };
-            ld8(p.r, rr); ld8(p.w, win); ld8(p.k, kin); ld8(p.v, vin); ld8(p.a, ain); ld8(p.g, gin);
+            auto ldq = [&](const __half* base) { return *reinterpret_cast<const int4*>(base + idx); };
+            auto ldc = [&](const __half* base) { return *reinterpret_cast<const int4*>(base + ch0); };
+            const int4 q_r = ldq(p.r), q_w = ldq(p.w), q_k = ldq(p.k), q_v = ldq(p.v), q_a = ldq(p.a), q_g = ldq(p.g);
+            int4 q_vg = q_v, q_vf = q_v;
             if (p.v_first) {
-                ld8(p.vgate, vg);
-                ld8(p.v_first, vf);
+                q_vg = ldq(p.vgate);
+                q_vf = ldq(p.v_first);
             }
-            float q[8], v2[8], ssq = 0.f, sbon = 0.f;
+            const int4 w_kk = ldc(p.k_k), w_ka = ldc(p.k_a), w_rk = ldc(p.r_k);
+            const __half2 *hr_ = reinterpret_cast<const __half2*>(&q_r), *hk = reinterpret_cast<const __half2*>(&q_k);
+            const __half2 *hv = reinterpret_cast<const __half2*>(&q_v), *ha = reinterpret_cast<const __half2*>(&q_a);
+            const __half2 *hvg = reinterpret_cast<const __half2*>(&q_vg), *hvf = reinterpret_cast<const __half2*>(&q_vf);
+            const __half2 *kkw = reinterpret_cast<const __half2*>(&w_kk), *kaw = reinterpret_cast<const __half2*>(&w_ka);
+            const __half2* rkw = reinterpret_cast<const __half2*>(&w_rk);
+            const __half* hw = reinterpret_cast<const __half*>(&q_w);
+            const __half2 one = __floats2half2_rn(1.f, 1.f);
+            __half2 q[4], v2[4];
+            float ssq = 0.f, sbon = 0.f;
 #pragma unroll
-            for (int e = 0; e < 8; e++) {
-                q[e] = hr(kin[e] * kk_w[e]);
-                k2[e] = hr(kin[e] * hr(1.0f + hr(hr(ain[e] - 1.0f) * ka_w[e])));
-                v2[e] = p.v_first ? hr(vin[e] + hr(hr(vf[e] - vin[e]) * vg[e])) : vin[e];
-                ssq += q[e] * q[e];
-                sbon += hr(hr(rr[e] * k2[e]) * rk_w[e]);
+            for (int u = 0; u < 4; u++) {
+                q[u] = __hmul2_rn(hk[u], kkw[u]);                                                           // k * k_k
+                k2[u] = __hmul2_rn(hk[u], __hadd2_rn(one, __hmul2_rn(__hsub2_rn(ha[u], one), kaw[u])));     // k * (1 + (a-1) * k_a)
+                v2[u] = p.v_first ? __hadd2_rn(hv[u], __hmul2_rn(__hsub2_rn(hvf[u], hv[u]), hvg[u])) : hv[u];
+                const float2 qf = __half22float2(q[u]);
+                ssq = fmaf(qf.x, qf.x, fmaf(qf.y, qf.y, ssq));
+                const float2 bf = __half22float2(__hmul2_rn(__hmul2_rn(hr_[u], k2[u]), rkw[u]));            // r * k * r_k
+                sbon += bf.x + bf.y;
+                rr[u] = hr_[u];
             }
 #pragma unroll
             for (int o = 1; o < 8; o <<= 1) {   // the 8 threads of a token are 8 consecutive lanes
                 ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
                 sbon += __shfl_xor_sync(0xffffffffu, sbon, o);
             }
-            const float nrm = hr(sqrtf(ssq));
-            __half v2h[8], gh[8];
+            const float rnrm = 1.0f / hr(sqrtf(ssq));
+            const __half2 zero2 = __floats2half2_rn(0.f, 0.f);
 #pragma unroll
-            for (int e = 0; e < 8; e++) {
-                const float kk = hr(q[e] / nrm);
-                a_vec[e] = -kk;
-                b_vec[e] = hr(kk * ain[e]);
-                const float wt = __half2float(decay_dither_c(__float2half_rn(win[e]), t_base + t));
-                ld[e] = __log2f(1.0f + wt);
+            for (int u = 0; u < 4; u++) {
+                const float2 qf = __half22float2(q[u]);
+                const __half2 kk = __floats2half2_rn(qf.x * rnrm, qf.y * rnrm);                            // normalize(k * k_k)
+                a_vec[u] = __hneg2(kk);
+                b_vec[u] = __hmul2_rn(kk, ha[u]);
+                ld[2 * u] = __log2f(1.0f + __half2float(decay_dither_c(hw[2 * u], t_base + t)));
+                ld[2 * u + 1] = __log2f(1.0f + __half2float(decay_dither_c(hw[2 * u + 1], t_base + t)));
                 if (!live) {   // past the end of the sequence: an identity step (d = 1, no update, no read-out)
-                    a_vec[e] = 0.f; b_vec[e] = 0.f; k2[e] = 0.f; v2[e] = 0.f; rr[e] = 0.f; ld[e] = 0.f;
+                    a_vec[u] = b_vec[u] = k2[u] = v2[u] = rr[u] = zero2;
+                    ld[2 * u] = ld[2 * u + 1] = 0.f;
                 }
-                v2h[e] = __float2half_rn(v2[e]);
-                gh[e] = __float2half_rn(gin[e]);
-                sm.L[tk][cg * 8 + e] = ld[e];
-                sm.vT[cg * 8 + e][tk] = v2h[e];
             }
-            *reinterpret_cast<int4*>(&sm.v2s[tk][cg * 8]) = *reinterpret_cast<const int4*>(v2h);
-            *reinterpret_cast<int4*>(&sm.gs[tk][cg * 8]) = *reinterpret_cast<const int4*>(gh);
+            *reinterpret_cast<float4*>(&sm.L[tk][cg * 8]) = make_float4(ld[0], ld[1], ld[2], ld[3]);
+            *reinterpret_cast<float4*>(&sm.L[tk][cg * 8 + 4]) = make_float4(ld[4], ld[5], ld[6], ld[7]);
+            *reinterpret_cast<int4*>(&sm.v2s[tk][cg * 8]) = *reinterpret_cast<const int4*>(v2);
+            *reinterpret_cast<int4*>(&sm.gs[tk][cg * 8]) = q_g;
             if (cg == 0) sm.bonus[tk] = hr(sbon);
         }
         __syncthreads();
@@ -212,23 +218,34 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
                 sm.L[s][tid] = c;
                 if (s == TC / 2 - 1) m = c;
             }
-            sm.em[tid] = exp2f(m);
-            sm.ecTm[tid] = exp2f(c - m);
+            sm.em[tid] = ex2_approx_ftz(m);
+            sm.ecTm[tid] = ex2_approx_ftz(c - m);
         }
         __syncthreads();
-        // ---- rescaled operands
+        // ---- rescaled operands (|c - m| <= 8 * 0.875: plain ex2.approx, no range handling needed)
         {
-            __half at[8], rt[8], bt[8], kt[8];
+            const float4 c0 = *reinterpret_cast<const float4*>(&sm.L[tk][cg * 8]), c1 = *reinterpret_cast<const float4*>(&sm.L[tk][cg * 8 + 4]);
+            const float4 m0 = *reinterpret_cast<const float4*>(&sm.L[TC / 2 - 1][cg * 8]);
+            const float4 m1 = *reinterpret_cast<const float4*>(&sm.L[TC / 2 - 1][cg * 8 + 4]);
+            const float cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+            const float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+            __half2 at[4], rt[4], bt[4], kt[4];
 #pragma unroll
-            for (int e = 0; e < 8; e++) {
-                const int j = cg * 8 + e;
-                const float c = sm.L[tk][j];
-                const float m = sm.L[TC / 2 - 1][j];
-                const float up = exp2f(c - m), dn = exp2f(m - c);
-                at[e] = __float2half_rn(a_vec[e] * exp2f(c - ld[e] - m));
-                rt[e] = __float2half_rn(rr[e] * up);
-                bt[e] = __float2half_rn(b_vec[e] * dn);
-                kt[e] = __float2half_rn(k2[e] * dn);
+            for (int u = 0; u < 4; u++) {
+                float up[2], dn[2], pv[2];
+#pragma unroll
+                for (int h2 = 0; h2 < 2; h2++) {
+                    const float d = cc[2 * u + h2] - mm[2 * u + h2];
+                    up[h2] = ex2_approx_ftz(d);
+                    dn[h2] = ex2_approx_ftz(-d);
+                    pv[h2] = ex2_approx_ftz(d - ld[2 * u + h2]);
+                }
+                const float2 af = __half22float2(a_vec[u]), rf = __half22float2(rr[u]);
+                const float2 bf = __half22float2(b_vec[u]), kf = __half22float2(k2[u]);
+                at[u] = __floats2half2_rn(af.x * pv[0], af.y * pv[1]);
+                rt[u] = __floats2half2_rn(rf.x * up[0], rf.y * up[1]);
+                bt[u] = __floats2half2_rn(bf.x * dn[0], bf.y * dn[1]);
+                kt[u] = __floats2half2_rn(kf.x * dn[0], kf.y * dn[1]);
             }
             *reinterpret_cast<int4*>(&sm.opT[tk][cg * 8]) = *reinterpret_cast<const int4*>(at);
             *reinterpret_cast<int4*>(&sm.opT[TC + tk][cg * 8]) = *reinterpret_cast<const int4*>(rt);
@@ -318,12 +335,10 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
 
         // ================================================================ 4. rhs -> U -> Y -> state (per warp: its 16 value rows)
         {
-            uint32_t va[4];   // V as A operand: rows i, k = s
+            uint32_t va[4];   // V as A operand (rows i, k = s) out of the token-major v' tile: transposed 8x8 loads
             const int i_lo = 16 * warp + g;
-            va[0] = lds32(&sm.vT[i_lo][2 * tq]);
-            va[1] = lds32(&sm.vT[i_lo + 8][2 * tq]);
-            va[2] = lds32(&sm.vT[i_lo][2 * tq + 8]);
-            va[3] = lds32(&sm.vT[i_lo + 8][2 * tq + 8]);
+            // matrices: (i 0-7, s 0-7), (i 8-15, s 0-7), (i 0-7, s 8-15), (i 8-15, s 8-15) of this warp's 16 rows
+            ldmatrix_x4_trans(va, &sm.v2s[(lane & 7) + 8 * (lane >> 4)][16 * warp + 8 * ((lane >> 3) & 1)]);
             // rhs = S0' A~ + V Aak
 #pragma unroll
             for (int nt = 0; nt < 2; nt++) mma16816(acc[nt], va, lds32(&sm.aakT[8 * nt + g][2 * tq]), lds32(&sm.aakT[8 * nt + g][2 * tq + 8]));
@@ -348,13 +363,10 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
             // S <- (S0' + U B~^T + V K~^T) diag(2^(c_16 - m))   (16 x 64 per warp, K = 32: s' = [u-tokens ; v-tokens])
 #pragma unroll
             for (int n = 0; n < 8; n++) {
-                const int j = 8 * n + g;
-                const uint32_t b0 = pack_u16(&sm.opS[2 * tq][j], &sm.opS[2 * tq + 1][j]);
-                const uint32_t b1 = pack_u16(&sm.opS[2 * tq + 8][j], &sm.opS[2 * tq + 9][j]);
-                mma16816(S[n], ua, b0, b1);
-                const uint32_t b2 = pack_u16(&sm.opS[TC + 2 * tq][j], &sm.opS[TC + 2 * tq + 1][j]);
-                const uint32_t b3 = pack_u16(&sm.opS[TC + 2 * tq + 8][j], &sm.opS[TC + 2 * tq + 9][j]);
-                mma16816(S[n], va, b2, b3);
+                uint32_t bq[4];   // B operand (k = s', n = j) out of the [s'][j] tile: rows s' = lane, columns 8n..8n+7
+                ldmatrix_x4_trans(bq, &sm.opS[lane][8 * n]);
+                mma16816(S[n], ua, bq[0], bq[1]);   // u-tokens x b~
+                mma16816(S[n], va, bq[2], bq[3]);   // v-tokens x k~
                 const float2 e = *reinterpret_cast<const float2*>(&sm.ecTm[8 * n + 2 * tq]);
                 S[n][0] *= e.x; S[n][1] *= e.y; S[n][2] *= e.x; S[n][3] *= e.y;
             }
@@ -363,13 +375,12 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
 
         // ================================================================ 5. GroupNorm (eps 64e-5) + bonus + gate (rwkv7.py:647-649)
         {
-            float y[8], s1 = 0.f, s2 = 0.f, ln_w[8], ln_b[8];
-            ldw8(p.ln_w, ln_w); ldw8(p.ln_b, ln_b);
+            float y[8], s1 = 0.f, s2 = 0.f;
 #pragma unroll
             for (int e = 0; e < 8; e++) {
                 y[e] = hr(sm.ys[tk][cg * 8 + e]);   // the WKV output is an fp16 tensor in the reference
                 s1 += y[e];
-                s2 += y[e] * y[e];
+                s2 = fmaf(y[e], y[e], s2);
             }
 #pragma unroll
             for (int o = 1; o < 8; o <<= 1) {
@@ -379,20 +390,22 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
             const float mean = s1 * (1.0f / 64.0f);
             const float var = fmaxf(s2 * (1.0f / 64.0f) - mean * mean, 0.0f);
             const float rstd = 1.0f / sqrtf(var + 64e-5f);
-            const float bonus = sm.bonus[tk];
+            const __half2 bonus = __float2half2_rn(sm.bonus[tk]);
             const int4 qv = *reinterpret_cast<const int4*>(&sm.v2s[tk][cg * 8]);
             const int4 qg = *reinterpret_cast<const int4*>(&sm.gs[tk][cg * 8]);
-            const __half *vh = reinterpret_cast<const __half*>(&qv), *gh = reinterpret_cast<const __half*>(&qg);
-            __half oh[8];
+            const int4 qlw = *reinterpret_cast<const int4*>(p.ln_w + ch0), qlb = *reinterpret_cast<const int4*>(p.ln_b + ch0);
+            const __half2 *vh = reinterpret_cast<const __half2*>(&qv), *gh = reinterpret_cast<const __half2*>(&qg);
+            const __half2 *lw = reinterpret_cast<const __half2*>(&qlw), *lb = reinterpret_cast<const __half2*>(&qlb);
+            __half2 oh[4];
 #pragma unroll
-            for (int e = 0; e < 8; e++) {
-                const float gn = hr((y[e] - mean) * rstd * ln_w[e] + ln_b[e]);
-                const float o = hr(gn + hr(bonus * __half2float(vh[e])));
-                oh[e] = __float2half_rn(hr(o * __half2float(gh[e])));
+            for (int u = 0; u < 4; u++) {
+                const float2 w2 = __half22float2(lw[u]), b2 = __half22float2(lb[u]);
+                const __half2 gn = __floats2half2_rn((y[2 * u] - mean) * rstd * w2.x + b2.x, (y[2 * u + 1] - mean) * rstd * w2.y + b2.y);
+                oh[u] = __hmul2_rn(__hadd2_rn(gn, __hmul2_rn(bonus, vh[u])), gh[u]);
             }
             if (live) *reinterpret_cast<int4*>(p.out + ((size_t)bb * T + t) * C + ch0) = *reinterpret_cast<const int4*>(oh);
         }
-        // the next chunk's prep writes L / vT / v2s / gs / bonus: every reader of those is past the barrier above except
+        // the next chunk's prep writes L / v2s / gs / bonus: every reader of those is past the barrier above except
         // this output stage, which reads ys / v2s / gs / bonus
         __syncthreads();
     }

@@ -71,12 +71,13 @@ def wkv7_forward_one(state, r, w, k, v, a, b, elapsed_t, slot_idx=None) -> torch
     return y.view(shp)
 
 
-def spmv_forward(vec: torch.Tensor, mat: torch.Tensor) -> torch.Tensor:
+def spmv_forward(vec: torch.Tensor, mat: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``SPMV_OP`` / ``rwkv_mm_sparsity`` (``Albatross/rwkv7.py:61-87``): vec (D,), mat (D,C) -> (C,)."""
     _req(vec, "vec")
     _req(mat, "mat")
     D, C = mat.shape
-    out = torch.empty((C,), dtype=torch.float16, device=vec.device)
+    if out is None:
+        out = torch.empty((C,), dtype=torch.float16, device=vec.device)
     rc = _lib.lib().b200_spmv_forward(D, C, vec.contiguous().data_ptr(), mat.contiguous().data_ptr(), out.data_ptr(),
                                       _stream(vec))
     _lib.check(rc, "b200_spmv_forward")

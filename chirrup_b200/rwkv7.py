@@ -35,7 +35,7 @@ _LW_ORDER = [
 ]
 
 
-_STEP_ENV = ("B200_UNFUSED_TMIX", "B200_NO_PDL", "B200_NO_PAIR", "B200_NO_DEFER", "B200_WKV_GENERIC", "B200_CHAIN", "B200_WKV_SEQUENTIAL")
+_STEP_ENV = ("B200_UNFUSED_TMIX", "B200_NO_PDL", "B200_NO_PAIR", "B200_NO_DEFER", "B200_WKV_GENERIC", "B200_CHAIN", "B200_WKV_SEQUENTIAL", "B200_NO_SPMV")
 
 
 def _stream(dev) -> int:
@@ -65,6 +65,7 @@ class RWKV_x070:
         self._graph_seen: Dict[tuple, int] = {}
         self._capture_stream = None
         self._gio = None
+        self._ffn_rows = None
         self.graph_hits = self.graph_misses = 0
         raw = state_dict if state_dict is not None else torch.load(args.MODEL_NAME + ".pth", map_location="cpu")
         self.n_head, self.head_size = raw["blocks.0.att.r_k"].shape          # rwkv7.py:173
@@ -344,8 +345,30 @@ class RWKV_x070:
             return self.forward_one(idx[0], state)
         return self.forward_one(idx, state)
 
+    def _ensure_ffn_value_rows(self) -> None:
+        """bsz-1 path only: ffn.value.weight once more in the reference's transformed (4C, C) layout (rwkv7.py:217-218), so
+        that ``RWKV_x070_CMix_one``'s ReLU^2-sparse product (rwkv7.py:653-662, ``rwkv_mm_sparsity`` / ``SPMV_OP``) can skip
+        the rows whose key activation is zero.  The batched path keeps the checkpoint's (C, 4C) = K-major layout for the
+        tensor-core GEMM; the second copy (4.3 GB at 7.2B) exists only once ``forward`` / ``forward_one`` has been called."""
+        if self._ffn_rows is not None:
+            return
+        rows = [self._w[f"blocks.{i}.ffn.value.weight"].t().contiguous() for i in range(self.n_layer)]
+        ptrs = (ctypes.c_void_p * len(rows))(*[t.data_ptr() for t in rows])
+        _lib.check(_lib.lib().b200_model_set_ffn_value_rows(self._handle, ptrs), "b200_model_set_ffn_value_rows")
+        self._ffn_rows = rows
+        for i, t in enumerate(rows):
+            self.z[f"blocks.{i}.ffn.value.weight"] = t
+        self._graphs.clear()
+        self._graph_seen.clear()
+
     def forward_one(self, idx: int, state):
-        """rwkv7.py:287-316 — one token, unbatched state; returns logits (V,)."""
+        """rwkv7.py:287-316 — one token, unbatched state; returns logits (V,).  The reference's ``forward_one(x, state)`` takes
+        the EMBEDDING VECTOR of the token (``forward`` looks it up, rwkv7.py:237-248); here the embedding gather is part of the
+        step, so this takes the token id — a (C,) tensor is rejected rather than misread."""
+        if torch.is_tensor(idx) and idx.numel() != 1:
+            raise TypeError("forward_one takes a token id here (the embedding lookup is inside the step); the reference's "
+                            "forward_one(x: (C,) embedding, state) form is not supported — call forward(token_id, state)")
+        self._ensure_ffn_value_rows()
         return self._step(self._tokens([int(idx)]), 1, 1, self._batched_view(state), False)[0]
 
     def forward_seq(self, idx: List[int], state, full_output: bool = False):

@@ -180,6 +180,12 @@ int b200_model_forward(b200_model* m, int B, int T, const int* tokens, void* sta
                        long s0_which_stride, void* state1, long s1_layer_stride, int n_slots, int* elapsed,
                        const int* slot_idx, void* logits, int full_output, void* workspace, long workspace_bytes,
                        void* stream);
+/* Optional: hand the model ffn.value.weight of every layer in the reference's transformed layout (F, C) row-major
+ * (Albatross/rwkv7.py:217-218 transposes it at load) — n_layer device pointers, or NULL to clear.  With it, a B = T = 1 step
+ * (forward / forward_one, RWKV_x070_CMix_one, rwkv7.py:653-662) runs its FFN value product as the ReLU^2-sparse
+ * vector x matrix product (b200_spmv_forward semantics: only rows with a non-zero key activation are read). */
+int b200_model_set_ffn_value_rows(b200_model* m, const void* const* ffn_value_fc);
+
 /* Greedy sampling of `rows` logit rows (fp16, V columns, row pitch ld): out[i] = lowest index of the row maximum (int32).
  * The top_k == 1 case of the worker's sampler (chirrup/worker.py:733-740, chirrup/utils/samplers.py:171-255). */
 int b200_argmax_f16(int rows, int V, const void* logits, long ld, int* out, void* stream);

@@ -159,6 +159,40 @@ def test_spmv_matches_exact_product():
     assert torch.count_nonzero(z) == 0
 
 
+@pytest.mark.parametrize("D,C,density", [(3072, 768, 0.2), (8192, 2048, 0.5), (16384, 4096, 0.1), (16384, 4096, 0.9), (4160, 264, 0.5),
+                                           (40, 64, 1.0)])
+def test_spmv_vs_reference_kernel_and_exact_product(D, C, density):
+    """The bsz-1 FFN value product (SURVEY a-6; 512 CTAs in clusters of 8 at C = 4096): against the exact fp32 product (one
+    rounding; ours must be within an fp16 ulp of it), against the REFERENCE'S OWN kernel spvecmatmul_noindices
+    (oracle/_ref, Albatross/cuda/rwkv7_state_fwd_fp16.cu:222-310; it accumulates in fp16 with atomics, so only to its own
+    noise), and bit-identical run to run — odd shapes, all-dense and very sparse vectors included."""
+    import os
+
+    from chirrup_b200 import ops
+    from oracle import rwkv7_oracle as O
+
+    g = torch.Generator().manual_seed(D + C)
+    vec = torch.randn(D, generator=g).abs() ** 2
+    vec[torch.rand(D, generator=g) > density] = 0
+    vec[D // 3] = -0.0                                                 # a negative zero is a zero (reference .cu:247-249)
+    vec = vec.half().cuda()
+    mat = (torch.randn(D, C, generator=g) * 0.05).half().cuda()
+    exact = (vec.float() @ mat.float())
+    a = ops.spmv_forward(vec, mat)
+    b = ops.spmv_forward(vec, mat)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b)
+    scale = exact.abs().max().clamp_min(1e-6)
+    assert ((a.float() - exact).abs().max() / scale) <= 1e-3
+    assert ((a.float() - exact).abs() <= exact.abs() * 2e-3 + 2e-4 * scale).all()                    # fp32 sums in another order
+    ref_so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libref_wkv7.so")
+    if os.path.exists(ref_so) and C % 256 == 0 and D % 64 == 0:       # the reference asserts these (.cu:325-326)
+        r = O.spmv_ref_cuda(vec, mat)
+        err_ref = float((r.float() - exact).abs().max() / scale)       # the reference's own fp16-accumulation noise
+        err_ours = float((a.float() - exact).abs().max() / scale)
+        assert err_ours <= err_ref + 1e-3 and float((a.float() - r.float()).abs().max() / scale) <= 2 * err_ref + 1e-3
+
+
 def test_linear_fuzz_random_shapes_and_epilogues():
     """60 seeded random problems across the three GEMM kernels (one CTA per tile for M <= 128, CTA pairs with K split for
     128 < M, persistent pairs for many M blocks): M, N, K with ragged tails (N, K multiples of 8 only), every epilogue; each

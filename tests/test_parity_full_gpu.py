@@ -62,13 +62,13 @@ def record(name, **kv):
     print(f"[parity-full {name}] " + "  ".join(f"{k}={v:.3e}" if isinstance(v, float) else f"{k}={v}" for k, v in kv.items()))
 
 
-def build_pair(geom_name, seed, recipe="trained_like", n_layer=None):
+def build_pair(geom_name, seed, recipe="trained_like", n_layer=None, margin=None):
     """Our model and the oracle's weight dict from the same seeded synthetic checkpoint, both resident on the GPU."""
     from chirrup_b200.rwkv7 import RWKV_x070, make_args
     from oracle import rwkv7_oracle as O
 
     geom = GEOMETRIES[geom_name]
-    raw = make_checkpoint(geom, seed=seed, recipe=recipe, n_layer=n_layer, device="cuda", dtype=torch.float16)
+    raw = make_checkpoint(geom, seed=seed, recipe=recipe, n_layer=n_layer, device="cuda", dtype=torch.float16, margin=margin)
     m = RWKV_x070(make_args(), state_dict={k: v.clone() for k, v in raw.items()})
     z = O.transform_checkpoint(raw, device="cuda")
     del raw
@@ -76,13 +76,13 @@ def build_pair(geom_name, seed, recipe="trained_like", n_layer=None):
     return geom, m, O, z, O.Geometry(z)
 
 
-def greedy_parity(name, geom_name, B, P, steps, seed, self_noise_every=1, strict=True):
+def greedy_parity(name, geom_name, B, P, steps, seed, self_noise_every=1, strict=True, margin=None):
     """Free-running greedy decode of our model against the oracle fed with ITS own tokens.  strict: every token of every row
     must be identical (north_star).  Not strict (configurations whose synthetic margin is not far above the fp16 noise): a
     differing arg-max is accepted only where the reference's own top-2 margin is within 4x the measured logit error of that
     row (a near-tie that the reference itself flips under a GEMM re-ordering), the row then continues on the reference's
     token, and the count is recorded."""
-    geom, m, O, z, og = build_pair(geom_name, seed)
+    geom, m, O, z, og = build_pair(geom_name, seed, margin=margin)
     g = torch.Generator().manual_seed(seed + 100)
     prompt = torch.randint(1, geom.vocab_size, (B, P), generator=g).tolist()
     st_a, st_b, st_c = m.generate_zero_state(B), O.zero_state(og, B, "cuda"), O.zero_state(og, B, "cuda")
@@ -144,8 +144,11 @@ def test_config1_1p5B_L24_bsz64_greedy_256_steps_token_identical():
 @needs_ref
 def test_config4_13p3B_L61_bsz512_greedy_steps():
     """BASELINE.json configs[4], full depth: 13.3B (L61, C4096), 512 rows = two 256-row M blocks in every GEMM, split-K over
-    several M blocks."""
-    greedy_parity("config4_13.3B_bsz512", "13.3B", B=512, P=4, steps=8, seed=43, strict=False)
+    several M blocks.  61 layers of O(0.15) residual updates wash out twice as much of the recipe's head alignment as 32 do: at the
+    default margin 0.5 % of the row-steps are near-ties that the reference itself flips under a GEMM re-ordering (first GPU run:
+    22 of 4096, every one within 4x the logit error), so this configuration uses a head margin of 24 instead of 12 and still
+    only accepts near-tie flips."""
+    greedy_parity("config4_13.3B_bsz512", "13.3B", B=512, P=4, steps=8, seed=43, strict=False, margin=24.0)
 
 
 @needs_ref

@@ -1,0 +1,22 @@
+set +e
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_parity_full_gpu.py -q -s -k "13p3B or bsz1 or plain" > gpurun_out/r02_parity_full_b.log 2>&1
+echo "rc=$?" >> gpurun_out/r02_parity_full_b.log
+timeout 900 python -m pytest tests/test_wkv_chunk_gpu.py tests/test_model_gpu.py tests/test_sampler_gpu.py tests/test_engine_gpu.py -q -s -m gpu > gpurun_out/r02_suite_b.log 2>&1
+echo "rc=$?" >> gpurun_out/r02_suite_b.log
+timeout 600 python bench.py --config prefill --steps 3 --warmup 1 > gpurun_out/r02_bench_prefill_v1.json 2> gpurun_out/r02_bench_prefill_v1.err
+timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/r02_bench_v2.json 2> gpurun_out/r02_bench_v2.err
+# ncu launch list of one prefill pass (chunk kernel share) and a full capture of the chunk kernel
+cat > /tmp/prefill_once.py <<'PY'
+import sys, torch
+sys.path.insert(0, '.')
+import bench
+geom, m = bench.build_model("7.2B", torch.device("cuda", 0))
+toks = torch.randint(1, geom.vocab_size, (32, 1024), generator=torch.Generator().manual_seed(0)).to(torch.int32)
+st = m.generate_zero_state(32)
+m.prefill(toks, st, chunk_len=512, want_logits=False)
+torch.cuda.synchronize()
+PY
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/r02_prefill_launches.csv python /tmp/prefill_once.py > gpurun_out/ncu1.log 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:wkv7_chunk_kernel -s 40 -c 1 -o gpurun_out/r02_wkv_chunk python /tmp/prefill_once.py > gpurun_out/ncu2.log 2>&1
+tail -3 gpurun_out/r02_parity_full_b.log gpurun_out/r02_suite_b.log
