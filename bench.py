@@ -453,10 +453,18 @@ def engine_run(geom_name: str, n_workers: int, slots: int, requests_per_worker: 
         dt = time.perf_counter() - t0
         eng.shutdown()
         per_worker = {k: v["decode_tokens"] for k, v in eng.worker_steps.items()}
-        return sum(counts), dt, t_load, per_worker
+        steady = {k: (slots * v["full_steps"] / v["full_time_s"] if v.get("full_time_s") else None) for k, v in eng.worker_steps.items()}
+        return sum(counts), dt, t_load, per_worker, steady, dict(eng.worker_steps)
 
-    n_tok, dt, t_load, per_worker = asyncio.run(main())
-    return {"value": n_tok / dt, "unit": "tok/s", "tokens": n_tok, "wall_s": dt, "workers": n_workers, "slots_per_worker": slots,
+    n_tok, dt, t_load, per_worker, steady, worker_stats = asyncio.run(main())
+    ok = [v for v in steady.values() if v]
+    gh = sum(v.get("graph_hits", 0) for v in worker_stats.values())
+    gm = sum(v.get("graph_misses", 0) for v in worker_stats.values())
+    return {"value": n_tok / dt, "steady_state_tok_per_s_per_worker": steady,
+            "step_graph_hit_rate": gh / max(1, gh + gm), "step_graph_hits": gh, "step_graph_misses": gm,
+            "steady_state_tok_per_s": sum(ok) if len(ok) == len(steady) and ok else None,
+            "steady_state_definition": "loops in which every slot of the worker took a decode step (no admission, no prefill chunk in "
+                                       "between): slots x such loops / their wall time, summed over workers", "unit": "tok/s", "tokens": n_tok, "wall_s": dt, "workers": n_workers, "slots_per_worker": slots,
             "requests": n_workers * requests_per_worker, "max_tokens": max_tokens, "load_s": t_load,
             "decode_tokens_per_worker_incl_warmup": per_worker,
             "api": "MPEngineCore.completion(prefill_tokens=...) async iteration: one worker process per GPU, one shared task "

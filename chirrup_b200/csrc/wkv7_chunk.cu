@@ -64,6 +64,13 @@ DEVI uint32_t pack2(float lo, float hi) {
     __half2 h = __floats2half2_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&h);
 }
+// 16-byte asynchronous global -> shared copy (LDGSTS): the next chunk's inputs travel while this chunk computes
+DEVI void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+DEVI void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+DEVI void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 DEVI uint32_t lds32(const __half* p) { return *reinterpret_cast<const uint32_t*>(p); }
 // four 8x8 b16 matrices, TRANSPOSED on the way in: lane l supplies the address of row (l & 7) of matrix (l >> 3); thread
 // (g, tq) receives elements (row 2tq, 2tq+1; column g) of each — the mma fragment of an operand stored k-major
@@ -96,6 +103,7 @@ struct ChunkSmem {
     alignas(16) __half v2s[TC][LDO];           // v' per token: A operand (via ldmatrix.trans) and output stage   [s][i]
     alignas(16) __half gs[TC][HS];
     float bonus[TC];
+    alignas(16) int4 stage[8][NT];             // next chunk's r,w,k,v,a,g,vgate,v_first rows: one private 16-byte slot per thread
     alignas(8) uint64_t bar;
 };
 
@@ -143,6 +151,26 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
         }
     }
 
+    // Each thread stages exactly the 8 x 16 bytes it will consume itself (token tk, channels 8cg..8cg+7 of r,w,k,v,a,g,vgate,
+    // v_first), so the prefetch needs no barrier: program order + cp.async.wait_group.  Tokens past T re-read token 0 (valid
+    // memory) and are masked below.
+    auto prefetch = [&](int t_first) {
+        const int tt = t_first + tk;
+        const size_t idx = ((size_t)bb * T + (tt < T ? tt : 0)) * C + ch0;
+        cp_async16(&sm.stage[0][tid], p.r + idx);
+        cp_async16(&sm.stage[1][tid], p.w + idx);
+        cp_async16(&sm.stage[2][tid], p.k + idx);
+        cp_async16(&sm.stage[3][tid], p.v + idx);
+        cp_async16(&sm.stage[4][tid], p.a + idx);
+        cp_async16(&sm.stage[5][tid], p.g + idx);
+        if (p.v_first) {
+            cp_async16(&sm.stage[6][tid], p.vgate + idx);
+            cp_async16(&sm.stage[7][tid], p.v_first + idx);
+        }
+        cp_async_commit();
+    };
+    prefetch(0);
+
     for (int t0 = 0; t0 < T; t0 += TC) {
         // ================================================================ 1. vector prep of 16 tokens (rwkv7.py:632-637)
         // Every reference op here acts on fp16 tensors (fp32 inside the op, one rounding): exactly one correctly rounded
@@ -152,15 +180,16 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
         __half2 a_vec[4], b_vec[4], k2[4], rr[4];
         float ld[8];
         {
-            const size_t idx = ((size_t)bb * T + (live ? t : 0)) * C + ch0;
-            auto ldq = [&](const __half* base) { return *reinterpret_cast<const int4*>(base + idx); };
             auto ldc = [&](const __half* base) { return *reinterpret_cast<const int4*>(base + ch0); };
-            const int4 q_r = ldq(p.r), q_w = ldq(p.w), q_k = ldq(p.k), q_v = ldq(p.v), q_a = ldq(p.a), q_g = ldq(p.g);
+            cp_async_wait_all();
+            const int4 q_r = sm.stage[0][tid], q_w = sm.stage[1][tid], q_k = sm.stage[2][tid], q_v = sm.stage[3][tid];
+            const int4 q_a = sm.stage[4][tid], q_g = sm.stage[5][tid];
             int4 q_vg = q_v, q_vf = q_v;
             if (p.v_first) {
-                q_vg = ldq(p.vgate);
-                q_vf = ldq(p.v_first);
+                q_vg = sm.stage[6][tid];
+                q_vf = sm.stage[7][tid];
             }
+            if (t0 + TC < T) prefetch(t0 + TC);   // this thread's slots are free again: the next chunk's rows start moving now
             const int4 w_kk = ldc(p.k_k), w_ka = ldc(p.k_a), w_rk = ldc(p.r_k);
             const __half2 *hr_ = reinterpret_cast<const __half2*>(&q_r), *hk = reinterpret_cast<const __half2*>(&q_k);
             const __half2 *hv = reinterpret_cast<const __half2*>(&q_v), *ha = reinterpret_cast<const __half2*>(&q_a);

@@ -173,7 +173,9 @@ class Worker:
         self.tokenizer = tokenizer or IdTokenizer()
         self.model = model
         self.slots: List[_Slot] = [_Slot() for _ in range(batch_size)]
-        self.steps = {"decode": 0, "prefill": 0, "decode_tokens": 0, "prefill_tokens": 0}
+        # full_steps / full_time_s: consecutive loops in which EVERY slot took a T = 1 step (the steady state of a loaded worker)
+        self.steps = {"decode": 0, "prefill": 0, "decode_tokens": 0, "prefill_tokens": 0, "full_steps": 0, "full_time_s": 0.0}
+        self._last_full = None
         self._occurrence = None                               # device penalty state, allocated with the first non-plain request
         self._occ_host = None
         self._par_dirty = False
@@ -600,6 +602,14 @@ class Worker:
         self._fill_task_pool()
         layout = group_slots(self.categories()) if self.perf_queue is not None else None   # the batch layout this loop runs
         n = self._run_forward_one()
+        if n == self.batch_size:
+            now = time.perf_counter()
+            if self._last_full is not None:
+                self.steps["full_steps"] += 1
+                self.steps["full_time_s"] += now - self._last_full
+            self._last_full = now
+        else:
+            self._last_full = None
         if self.steps["decode"] % self.decode_prefill_ratio == 0 or n == 0:      # worker.py:854-856
             n += self._run_forward_seq()
         if n:

@@ -118,7 +118,10 @@ def _worker_main(worker_id: str, gpu_id: int, model_config: ModelLoadConfig, bat
                 while True:
                     msg = ctrl_q.get_nowait()
                     if msg[0] == "shutdown":
-                        result_q.put(("worker_exit", worker_id, dict(w.steps)))
+                        stats = dict(w.steps)
+                        stats["graph_hits"] = getattr(w.model, "graph_hits", 0)      # decode steps replayed from a step graph
+                        stats["graph_misses"] = getattr(w.model, "graph_misses", 0)  # ... launched eagerly (or captured)
+                        result_q.put(("worker_exit", worker_id, stats))
                         return
                     if msg[0] == "abort" and msg[1] in by_id:
                         by_id[msg[1]].task_event_queue.put("abort")

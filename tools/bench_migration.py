@@ -17,6 +17,9 @@ import bench
 from chirrup_b200 import ops, state_move
 
 
+N_STREAMS = int(os.environ.get("B200_MIG_STREAMS", "1"))   # slot copies of one direction spread over this many streams
+
+
 class Replica:
     def __init__(self, dev: int, geom_name: str, slots: int, spare: int):
         self.dev = torch.device(f"cuda:{dev}")
@@ -34,6 +37,7 @@ class Replica:
             self.nxt = torch.empty((slots,), dtype=torch.int32, device=self.dev)
             self.stream = torch.cuda.Stream(self.dev)
             self.mig = torch.cuda.Stream(self.dev)
+            self.migs = [self.mig] + [torch.cuda.Stream(self.dev) for _ in range(max(0, N_STREAMS - 1))]
             self.m.graph_decode = False      # this tool captures the whole step (forward + argmax + feedback) itself
             with torch.cuda.stream(self.stream):
                 for _ in range(2):
@@ -79,12 +83,17 @@ def decode_phase(reps, steps, per_step, slots, spare):
         if per_step:
             for d, r in enumerate(reps):            # destination d pulls spare slots from the other replica
                 src = reps[1 - d]
-                with torch.cuda.device(r.dev), torch.cuda.stream(r.mig):
+                with torch.cuda.device(r.dev):
                     m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     m0.record(r.mig)
+                    for st in r.migs[1:]:
+                        st.wait_event(m0)
                     for j in range(per_step):
-                        b = state_move.migrate_slot(src.state, slots + ((k + j) % spare), r.state, slots + ((k + j + 1) % spare))
+                        with torch.cuda.stream(r.migs[j % len(r.migs)]):
+                            b = state_move.migrate_slot(src.state, slots + ((k + j) % spare), r.state, slots + ((k + j + 1) % spare))
                         moved += b if d == 0 else 0
+                    for st in r.migs[1:]:
+                        r.mig.wait_stream(st)
                     m1.record(r.mig)
                     batch.append((m0, m1))
             k += per_step
@@ -123,11 +132,16 @@ def main():
     mev = []
     t0 = time.perf_counter()
     for d, r in enumerate(reps):
-        with torch.cuda.device(r.dev), torch.cuda.stream(r.mig):
+        with torch.cuda.device(r.dev):
             m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             m0.record(r.mig)
+            for st in r.migs[1:]:
+                st.wait_event(m0)
             for i in range(n):
-                state_move.migrate_slot(reps[1 - d].state, a.slots + i % a.spare, r.state, a.slots + (i + 1) % a.spare)
+                with torch.cuda.stream(r.migs[i % len(r.migs)]):
+                    state_move.migrate_slot(reps[1 - d].state, a.slots + i % a.spare, r.state, a.slots + (i + 1) % a.spare)
+            for st in r.migs[1:]:
+                r.mig.wait_stream(st)
             m1.record(r.mig)
             mev.append((m0, m1))
     t_enq = time.perf_counter() - t0
@@ -141,7 +155,8 @@ def main():
     out = {
         "config": f"{a.geom} geometry, {a.slots} decode slots per GPU (+{a.spare} spare), 2 GPUs, greedy decode from a CUDA graph per GPU; "
                   f"migration = {a.per_step} slots per decode step per direction, {slot_b / 2**20:.1f} MiB each, b200_slot_copy (peer DMA)",
-        "p2p_access": bool(torch.cuda.can_device_access_peer(0, 1)),
+        "p2p_access": bool(torch.cuda.can_device_access_peer(0, 1)), "streams_per_direction": N_STREAMS,
+        "slot_copy_mode": os.environ.get("B200_SLOT_COPY", "copy engine (cudaMemcpy2DAsync)"),
         "slot_MiB": slot_b / 2**20,
         "migration_alone_GBps_per_direction": alone_gbps,
         "migration_alone_us_per_slot_device": [m / n * 1e3 for m in alone_ms],
