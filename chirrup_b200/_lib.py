@@ -41,6 +41,7 @@ SIGNATURES: Dict[str, tuple] = {
     "b200_argmax_f16": (_I, [_I, _I, _P, _L, _P, _P]),
     "b200_sample_f16": (_I, [_I, _I, _P, _L, _P, _P, _P]),
     "b200_slot_copy": (_I, [_P, _L, _P, _L, _L, _L, _P]),
+    "b200_slot_move": (_I, [_P, _L, _P, _L, _L, _L, _P, _L, _P, _L, _L, _L, _P, _P, _P]),
 }
 
 

@@ -330,6 +330,23 @@ __global__ void __launch_bounds__(256) slot_copy_kernel(uint8_t* __restrict__ ds
 }  // namespace
 }  // namespace b200
 
+extern "C" int b200_slot_copy(void* dst, long dst_pitch, const void* src, long src_pitch, long width_bytes, long rows, void* stream);
+
+// One request's whole state in ONE call: the L WKV tiles, the 2L shift rows and the elapsed counter (three async copies).
+// The Python-side cost of a migration (three ctypes calls + stream bookkeeping, ~100 us) was what capped round 1's
+// 330-350 GB/s: the copy engine needs ~45 us for a 31.5 MiB slot.
+extern "C" int b200_slot_move(void* dst1, long dst1_pitch, const void* src1, long src1_pitch, long width1, long rows1, void* dst0,
+                              long dst0_pitch, const void* src0, long src0_pitch, long width0, long rows0, int* dst_elapsed,
+                              const int* src_elapsed, void* stream) {
+    int rc = b200_slot_copy(dst1, dst1_pitch, src1, src1_pitch, width1, rows1, stream);
+    if (rc) return rc;
+    rc = b200_slot_copy(dst0, dst0_pitch, src0, src0_pitch, width0, rows0, stream);
+    if (rc) return rc;
+    if (dst_elapsed && src_elapsed)
+        rc = (int)cudaMemcpyAsync(dst_elapsed, src_elapsed, sizeof(int), cudaMemcpyDefault, static_cast<cudaStream_t>(stream));
+    return rc;
+}
+
 extern "C" int b200_slot_copy(void* dst, long dst_pitch, const void* src, long src_pitch, long width_bytes, long rows,
                               void* stream) {
     if (!dst || !src || width_bytes < 0 || rows < 0 || dst_pitch < width_bytes || src_pitch < width_bytes) return B200_ERR_BAD_ARG;

@@ -232,6 +232,12 @@ int b200_sample_f16(int rows, int V, void* logits, long ld, const b200_sample_pa
  * (slot -> CPU), :586-597 (CPU -> slot), :304-360 (swap).  state[1] of slot s: dst = base + s*H*64*64*2, pitch =
  * n_slots*H*64*64*2, width = H*64*64*2, rows = L;  state[0]: pitch = n_slots*C*2, width = C*2, rows = 2L. */
 int b200_slot_copy(void* dst, long dst_pitch, const void* src, long src_pitch, long width_bytes, long rows, void* stream);
+/* A whole request in one call: b200_slot_copy of its state[1] rows (…1), of its state[0] rows (…0) and the 4-byte copy of its
+ * elapsed counter (skipped when either pointer is NULL).  chirrup/worker.py:591-597 (admission) / :427-429 (extraction) for
+ * all three state tensors at once; between two workers' GPUs this is the NVLink migration of BASELINE configs[4]. */
+int b200_slot_move(void* dst1, long dst1_pitch, const void* src1, long src1_pitch, long width1, long rows1, void* dst0,
+                   long dst0_pitch, const void* src0, long src0_pitch, long width0, long rows0, int* dst_elapsed,
+                   const int* src_elapsed, void* stream);
 
 /* Number of kernels the last b200_model_forward on this model launched (bench.py reports it as gpu_launches). */
 int b200_model_last_launch_count(const b200_model* m);

@@ -268,3 +268,30 @@ def test_state_cache_hit_inside_the_engine_matches_cold_run():
     assert entry[0].is_cuda and int(entry[2][0]) == len(prompt) - pad          # GPU-resident tier; elapsed = tokens consumed
     # prefill work: 180 (cold) + 3 (b: padding only) + 28 (c: padding + extension), none of the cached 177 tokens twice
     assert stats["prefill_tokens"] <= 180 + 3 + 28
+
+
+def test_batched_slot_migration_equals_slot_by_slot():
+    """state_move.migrate_slots (one b200_slot_move call per slot, one ordering event per batch) moves exactly the bytes
+    migrate_slot moves — on one GPU here; between peers when two are visible."""
+    from chirrup_b200 import state_move
+
+    geom, m = _model()
+    devs = ["cuda:0", "cuda:1" if torch.cuda.device_count() > 1 else "cuda:0"]
+    a = m.generate_zero_state(6)
+    for t in a[:2]:
+        t.normal_(0, 1)
+    a[2].copy_(torch.arange(6, dtype=torch.int32) * 7 + 3)
+    b1 = [torch.zeros_like(t, device=devs[1]) for t in a]
+    b2 = [torch.zeros_like(t, device=devs[1]) for t in a]
+    src, dst = [4, 0, 2], [1, 5, 3]
+    moved = state_move.migrate_slots(a, src, b1, dst)
+    for s_, d_ in zip(src, dst):
+        state_move.migrate_slot(a, s_, b2, d_)
+    for dev in set(devs):
+        torch.cuda.synchronize(dev)
+    assert moved == 3 * state_move.slot_bytes(a)
+    for x, y in zip(b1, b2):
+        assert torch.equal(x.cpu(), y.cpu())
+    for s_, d_ in zip(src, dst):
+        assert torch.equal(b1[1][:, d_].cpu(), a[1][:, s_].cpu()) and int(b1[2][d_]) == int(a[2][s_])
+    assert torch.count_nonzero(b1[1][:, 0]) == 0 and torch.count_nonzero(b1[0][:, :, 2]) == 0        # other slots untouched

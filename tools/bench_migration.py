@@ -17,6 +17,7 @@ import bench
 from chirrup_b200 import ops, state_move
 
 
+BATCHED = os.environ.get("B200_MIG_UNBATCHED") is None      # state_move.migrate_slots (one C call per slot) vs migrate_slot
 N_STREAMS = int(os.environ.get("B200_MIG_STREAMS", "1"))   # slot copies of one direction spread over this many streams
 
 
@@ -88,9 +89,15 @@ def decode_phase(reps, steps, per_step, slots, spare):
                     m0.record(r.mig)
                     for st in r.migs[1:]:
                         st.wait_event(m0)
-                    for j in range(per_step):
-                        with torch.cuda.stream(r.migs[j % len(r.migs)]):
-                            b = state_move.migrate_slot(src.state, slots + ((k + j) % spare), r.state, slots + ((k + j + 1) % spare))
+                    for si, st in enumerate(r.migs):
+                        idx = list(range(si, per_step, len(r.migs)))
+                        with torch.cuda.stream(st):
+                            if BATCHED:
+                                b = state_move.migrate_slots(src.state, [slots + ((k + j) % spare) for j in idx], r.state,
+                                                             [slots + ((k + j + 1) % spare) for j in idx])
+                            else:
+                                b = sum(state_move.migrate_slot(src.state, slots + ((k + j) % spare), r.state,
+                                                                slots + ((k + j + 1) % spare)) for j in idx)
                         moved += b if d == 0 else 0
                     for st in r.migs[1:]:
                         r.mig.wait_stream(st)
@@ -137,9 +144,15 @@ def main():
             m0.record(r.mig)
             for st in r.migs[1:]:
                 st.wait_event(m0)
-            for i in range(n):
-                with torch.cuda.stream(r.migs[i % len(r.migs)]):
-                    state_move.migrate_slot(reps[1 - d].state, a.slots + i % a.spare, r.state, a.slots + (i + 1) % a.spare)
+            for si, st in enumerate(r.migs):
+                idx = list(range(si, n, len(r.migs)))
+                with torch.cuda.stream(st):
+                    if BATCHED:
+                        state_move.migrate_slots(reps[1 - d].state, [a.slots + i % a.spare for i in idx], r.state,
+                                                 [a.slots + (i + 1) % a.spare for i in idx])
+                    else:
+                        for i in idx:
+                            state_move.migrate_slot(reps[1 - d].state, a.slots + i % a.spare, r.state, a.slots + (i + 1) % a.spare)
             for st in r.migs[1:]:
                 r.mig.wait_stream(st)
             m1.record(r.mig)
@@ -148,6 +161,27 @@ def main():
     sync_all(reps)
     alone_ms = [m0.elapsed_time(m1) for m0, m1 in mev]
     alone_gbps = [n * slot_b / (m * 1e-3) * 1e-9 for m in alone_ms]
+    # the link's own ceiling for this message size: contiguous 32 MiB peer copies (copy engine), one way and both ways at once
+    def ceiling(both):
+        bufs = []
+        for d in (0, 1):
+            with torch.cuda.device(reps[d].dev):
+                bufs.append((torch.empty(32 << 20, dtype=torch.uint8, device=reps[d].dev), torch.empty(32 << 20, dtype=torch.uint8, device=reps[d].dev)))
+        sync_all(reps)
+        evs = []
+        for d in ((0, 1) if both else (0,)):
+            r = reps[d]
+            with torch.cuda.device(r.dev), torch.cuda.stream(r.mig):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(r.mig)
+                for _ in range(32):
+                    bufs[d][0].copy_(bufs[1 - d][1], non_blocking=True)      # destination pulls from the peer
+                e1.record(r.mig)
+                evs.append((e0, e1))
+        sync_all(reps)
+        return [32 * (32 << 20) / (e0.elapsed_time(e1) * 1e-3) * 1e-9 for e0, e1 in evs]
+
+    ceil_one, ceil_both = ceiling(False), ceiling(True)
     # decode alone, then decode under migration
     decode_phase(reps, 5, 0, a.slots, a.spare)
     ms0, _, _ = decode_phase(reps, a.steps, 0, a.slots, a.spare)
@@ -155,10 +189,11 @@ def main():
     out = {
         "config": f"{a.geom} geometry, {a.slots} decode slots per GPU (+{a.spare} spare), 2 GPUs, greedy decode from a CUDA graph per GPU; "
                   f"migration = {a.per_step} slots per decode step per direction, {slot_b / 2**20:.1f} MiB each, b200_slot_copy (peer DMA)",
-        "p2p_access": bool(torch.cuda.can_device_access_peer(0, 1)), "streams_per_direction": N_STREAMS,
+        "p2p_access": bool(torch.cuda.can_device_access_peer(0, 1)), "streams_per_direction": N_STREAMS, "host_path": "migrate_slots (b200_slot_move)" if BATCHED else "migrate_slot",
         "slot_copy_mode": os.environ.get("B200_SLOT_COPY", "copy engine (cudaMemcpy2DAsync)"),
         "slot_MiB": slot_b / 2**20,
         "migration_alone_GBps_per_direction": alone_gbps,
+        "link_ceiling_contiguous_32MiB_copies_GBps": {"one_way": ceil_one, "both_ways_at_once_per_direction": ceil_both},
         "migration_alone_us_per_slot_device": [m / n * 1e3 for m in alone_ms],
         "migration_host_enqueue_us_per_slot": t_enq / (2 * n) * 1e6,
         "decode_alone_ms_per_step": [m / a.steps for m in ms0],
