@@ -895,7 +895,8 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
     const bool fixed256 = force_bn != 0;
     int best_s = 1, best_bn[PAIR_MAX_GROUP];
     double best_cost = 1e30;
-    const int cands[4] = {force_bn ? force_bn : 256, 192, 128, 64};
+    // 224: FFN key (N = 16384) then has 74 tiles = one per CTA pair, each 7/8 as wide, instead of 64 tiles on 64 of 74 pairs
+    const int cands[5] = {force_bn ? force_bn : 256, 224, 192, 128, 64};
     for (int s = 1; s <= PAIR_MAX_SPLIT; s++) {
         if (s > 1 && s > min_kb / 2) break;
         if (force_s && s != force_s && force_s <= min_kb / 2) continue;
@@ -906,7 +907,7 @@ int pair_group_launch(int n, const LinearDesc* d, int M, void* workspace, long w
         }
         if (!ok) continue;
         const int slots = pair_slots(s);
-        for (int ci = 0; ci < (fixed256 ? 1 : 4); ci++) {
+        for (int ci = 0; ci < (fixed256 ? 1 : 5); ci++) {
             int bns[PAIR_MAX_GROUP];
             long tiles = 0;
             double worst = 0.0;

@@ -296,40 +296,6 @@ extern "C" int b200_argmax_f16(int rows, int V, const void* logits, long ld, int
     return launch_argmax_rows(rows, V, static_cast<const __half*>(logits), ld, out, static_cast<cudaStream_t>(stream));
 }
 
-namespace b200 {
-namespace {
-// Strided slot copy as a kernel: 16-byte loads from `src` (possibly a PEER GPU's memory, read over NVLink) and 16-byte stores
-// to local memory, every CTA walking the rows with a grid stride and 4 independent 16-byte transactions per thread in
-// flight.  The copy engine's 2-D path moves 61 x 512 KiB rows at 330-360 GB/s between peers (profiles/r01_migration_config5.json);
-// a few dozen CTAs pulling with wide loads keep far more of the link busy.  Used only between two device pointers with
-// 16-byte-aligned rows; everything else (host tiers, odd alignments) stays on cudaMemcpy2DAsync.
-__global__ void __launch_bounds__(256) slot_copy_kernel(uint8_t* __restrict__ dst, long dst_pitch, const uint8_t* __restrict__ src,
-                                                        long src_pitch, long width16, long rows) {
-    const long per_row = width16;                       // int4 per row
-    const long total = per_row * rows;
-    const long stride = (long)gridDim.x * blockDim.x;
-    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    for (; i + 3 * stride < total; i += 4 * stride) {
-        int4 v[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const long e = i + u * stride, r = e / per_row, c = e - r * per_row;
-            v[u] = __ldcs(reinterpret_cast<const int4*>(src + r * src_pitch) + c);
-        }
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const long e = i + u * stride, r = e / per_row, c = e - r * per_row;
-            reinterpret_cast<int4*>(dst + r * dst_pitch)[c] = v[u];
-        }
-    }
-    for (; i < total; i += stride) {
-        const long r = i / per_row, c = i - r * per_row;
-        reinterpret_cast<int4*>(dst + r * dst_pitch)[c] = __ldcs(reinterpret_cast<const int4*>(src + r * src_pitch) + c);
-    }
-}
-}  // namespace
-}  // namespace b200
-
 extern "C" int b200_slot_copy(void* dst, long dst_pitch, const void* src, long src_pitch, long width_bytes, long rows, void* stream);
 
 // One request's whole state in ONE call: the L WKV tiles, the 2L shift rows and the elapsed counter (three async copies).
@@ -351,22 +317,9 @@ extern "C" int b200_slot_copy(void* dst, long dst_pitch, const void* src, long s
                               void* stream) {
     if (!dst || !src || width_bytes < 0 || rows < 0 || dst_pitch < width_bytes || src_pitch < width_bytes) return B200_ERR_BAD_ARG;
     if (width_bytes == 0 || rows == 0) return 0;
-    // B200_SLOT_COPY=kernel: pull with an SM copy kernel when both ends are device memory (peer or local) and 16-byte aligned;
-    // default: the copy engine (no SM work at all under a decode step)
-    static const char* mode = getenv("B200_SLOT_COPY");
-    if (mode && mode[0] == 'k' &&
-        !((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src) | (uintptr_t)dst_pitch | (uintptr_t)src_pitch |
-           (uintptr_t)width_bytes) & 15)) {
-        cudaPointerAttributes ad, as;
-        if (cudaPointerGetAttributes(&ad, dst) == cudaSuccess && cudaPointerGetAttributes(&as, src) == cudaSuccess &&
-            ad.type == cudaMemoryTypeDevice && as.type == cudaMemoryTypeDevice) {
-            static const int n_cta = getenv("B200_SLOT_COPY_CTAS") ? atoi(getenv("B200_SLOT_COPY_CTAS")) : 64;
-            b200::slot_copy_kernel<<<n_cta, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-                static_cast<uint8_t*>(dst), dst_pitch, static_cast<const uint8_t*>(src), src_pitch, width_bytes / 16, rows);
-            return (int)cudaGetLastError();
-        }
-        cudaGetLastError();
-    }
+    // (an SM pull kernel with 16-byte peer loads was measured against this: 268-370 GB/s alone and 76-136 GB/s under a decode
+    // step vs 400 / 330-350 GB/s for the copy engine, which also costs the decode step nothing — rejected,
+    // profiles/r02_migration_config5_pull_kernel_64cta_rejected.json)
     return (int)cudaMemcpy2DAsync(dst, (size_t)dst_pitch, src, (size_t)src_pitch, (size_t)width_bytes, (size_t)rows,
                                   cudaMemcpyDefault, static_cast<cudaStream_t>(stream));
 }

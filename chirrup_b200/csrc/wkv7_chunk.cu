@@ -88,9 +88,19 @@ DEVI void mma16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t 
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+// 39 KB per CTA: five CTAs (20 warps) per SM, which also turns the 2 048 (sequence, head) tiles of a bsz-32 launch into three
+// rounds of 740 instead of four rounds of 592.  Two regions are time-shared: the TMA state tile is only live before the first
+// and after the last chunk, the input staging slots only in between; the cumulative decays (L) are dead once the operands
+// are rescaled, the chunk's y tile is born after that.
 struct ChunkSmem {
-    alignas(1024) uint8_t tile[HS * HS * 2];   // state tile, TMA SWIZZLE_128B layout
-    float L[TC][HS];                           // log2 d, then its inclusive cumulative sum over the chunk's tokens
+    union alignas(1024) {
+        uint8_t tile[HS * HS * 2];             // state tile, TMA SWIZZLE_128B layout (launch prologue / epilogue)
+        int4 stage[8][NT];                     // next chunk's r,w,k,v,a,g,vgate,v_first rows: one private 16-byte slot per thread
+    };
+    union {
+        float L[TC][HS];                       // log2 d, then its inclusive cumulative sum over the chunk's tokens (stages 1-3)
+        float ys[TC][LDY];                     // y of the chunk [t][i] (stages 4-5)
+    };
     float em[HS], ecTm[HS];                    // 2^m, 2^(c_16 - m) per channel
     alignas(16) __half opT[2 * TC][LDO];       // rows 0..15 a~_t, rows 16..31 r~_t           [t][j]
     alignas(16) __half opS[2 * TC][LDO];       // rows 0..15 b~_s, rows 16..31 k~_s           [s][j]
@@ -99,15 +109,13 @@ struct ChunkSmem {
     alignas(16) __half akrT[TC][LDS16];
     alignas(16) __half tinvT[TC][LDS16];
     float aab[TC][TC + 1];                     // Aab in fp32 for the triangular inverse      [s][t]
-    float ys[TC][LDY];                         // y of the chunk                               [t][i]
     alignas(16) __half v2s[TC][LDO];           // v' per token: A operand (via ldmatrix.trans) and output stage   [s][i]
     alignas(16) __half gs[TC][HS];
     float bonus[TC];
-    alignas(16) int4 stage[8][NT];             // next chunk's r,w,k,v,a,g,vgate,v_first rows: one private 16-byte slot per thread
     alignas(8) uint64_t bar;
 };
 
-__global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant__ CUtensorMap tm_state, const WkvFusedArgs p) {
+__global__ void __launch_bounds__(NT, 5) wkv7_chunk_kernel(const __grid_constant__ CUtensorMap tm_state, const WkvFusedArgs p) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     ChunkSmem& sm = *reinterpret_cast<ChunkSmem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));   // TMA swizzle atom alignment
 
@@ -169,6 +177,7 @@ __global__ void __launch_bounds__(NT, 4) wkv7_chunk_kernel(const __grid_constant
         }
         cp_async_commit();
     };
+    __syncthreads();   // every thread has taken its part of the state tile: the region becomes the staging slots
     prefetch(0);
 
     for (int t0 = 0; t0 < T; t0 += TC) {

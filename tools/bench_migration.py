@@ -190,7 +190,7 @@ def main():
         "config": f"{a.geom} geometry, {a.slots} decode slots per GPU (+{a.spare} spare), 2 GPUs, greedy decode from a CUDA graph per GPU; "
                   f"migration = {a.per_step} slots per decode step per direction, {slot_b / 2**20:.1f} MiB each, b200_slot_copy (peer DMA)",
         "p2p_access": bool(torch.cuda.can_device_access_peer(0, 1)), "streams_per_direction": N_STREAMS, "host_path": "migrate_slots (b200_slot_move)" if BATCHED else "migrate_slot",
-        "slot_copy_mode": os.environ.get("B200_SLOT_COPY", "copy engine (cudaMemcpy2DAsync)"),
+        "slot_copy_mode": "copy engine (cudaMemcpy2DAsync)",
         "slot_MiB": slot_b / 2**20,
         "migration_alone_GBps_per_direction": alone_gbps,
         "link_ceiling_contiguous_32MiB_copies_GBps": {"one_way": ceil_one, "both_ways_at_once_per_direction": ceil_both},
