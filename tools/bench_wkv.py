@@ -58,10 +58,20 @@ def main():
                 fn()
             torch.cuda.synchronize()
             ms = (time.perf_counter() - t0) * 1e3 / a.iters
-        else:
+        else:                              # graph replay: the per-launch Python cost (~15 us) must not be what is timed
+            g = torch.cuda.CUDAGraph()
+            st = torch.cuda.Stream()
+            st.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(st):
+                fn()
+                with torch.cuda.graph(g, stream=st):
+                    fn()
+            torch.cuda.current_stream().wait_stream(st)
+            g.replay()
+            torch.cuda.synchronize()
             s.record()
             for _ in range(a.iters):
-                fn()
+                g.replay()
             e.record()
             torch.cuda.synchronize()
             ms = s.elapsed_time(e) / a.iters
