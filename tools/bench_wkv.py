@@ -51,13 +51,14 @@ def main():
             fn()
         torch.cuda.synchronize()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        if name == "reference_kernel":   # launches on the legacy default stream (reference .cu:315)
-            import time
-            t0 = time.perf_counter()
+        if name == "reference_kernel":   # launches on the legacy default stream (reference .cu:315) = torch's default stream:
+            ds = torch.cuda.default_stream()          # events there bracket them; the launches cannot be graph-captured
+            s.record(ds)
             for _ in range(a.iters):
                 fn()
+            e.record(ds)
             torch.cuda.synchronize()
-            ms = (time.perf_counter() - t0) * 1e3 / a.iters
+            ms = s.elapsed_time(e) / a.iters
         else:                              # graph replay: the per-launch Python cost (~15 us) must not be what is timed
             g = torch.cuda.CUDAGraph()
             st = torch.cuda.Stream()
