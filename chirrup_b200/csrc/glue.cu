@@ -97,133 +97,187 @@ __global__ void embed_gather_kernel(int M, int C, int V, const int* __restrict__
         *reinterpret_cast<int4*>(dst + c) = __ldg(reinterpret_cast<const int4*>(src + c));
 }
 
-// Sum of one float per thread over the block; every warp reduces the per-warp partials itself, so one barrier per call.
-// `part` must be a buffer (32 floats) not used by the previous block_sum1 call.
-DEVI float block_sum1(float v, float* part) {
-    v = warp_sum(v);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    if (lane == 0) part[warp] = v;
-    __syncthreads();
-    return warp_sum(lane < nw ? part[lane] : 0.f);
-}
+// LayerNorm -> token shift -> NMIX lerps for a STRIP of consecutive tokens of one sequence per CTA:
+//   cur = LN(x[b,t]);  prev = t ? LN(x[b,t-1]) : shift_state[b];  out_n[b,t] = cur + (prev - cur) * mix_n;  shift_state[b] <- LN(x[b,T-1])
+// 128 threads per CTA, up to four 8-channel chunks per thread (C <= 4096), 64 registers: eight CTAs = eight independent rows
+// in flight per SM, each reduction a barrier among four warps only.  (Round 1 ran one 512-thread CTA per row, two per SM, and
+// for T > 1 normalised every row twice — once as `cur`, once as the next token's `prev`: 333 + 231 us per layer at 16 384
+// tokens, 1.2-2.8 TB/s, as much as the chunked WKV kernel.)  A strip keeps the previous token's LN in registers, so each row is
+// loaded and normalised once; only the strip's first token re-normalises its predecessor.  The strip that holds token 0 owns
+// the sequence's shift-state row: it reads the old value (before griddepcontrol.wait: it is last written by this kernel one
+// step earlier) and stores LN(x[b,T-1]) — computing that row itself when it lies in another strip, so no CTA depends on another.
+// Decode (T = 1, strip = 1) may first finish the producing GEMM's deferred K split (glue.h): x <- fp16(x + fp16(p_0 + p_1 + ...)).
+// Two shapes of the same kernel: prefill (T > 1) runs 128 threads x four 8-channel chunks per thread as described; a decode
+// step (T = 1: 256 rows, at most two CTAs per SM whatever their size) keeps round 1's 512 threads x one chunk, where the row's
+// latency, not the number of rows in flight, is what counts.
+template <int LN_K>
+struct RowQ {   // one row's share of this thread, packed fp16 (converted where it is used)
+    int4 q[LN_K];
+};
 
-// LayerNorm (eps 1e-5, two-pass fp32 statistics as ATen) of one row held as 8 values per active thread, affine parameters
-// already in registers; result rounded to fp16.  Uses red[0..31] and red[32..63].
-DEVI H8 layer_norm8_pre(const H8& x, bool active, int C, const int4& wq, const int4& bq, float* red) {
-    float s = 0.f;
-    if (active) {
+// fp32 two-pass statistics (as ATen) of a row spread over the CTA; `red` = 2 x 16 floats not used by the previous two calls.
+// The summation tree is the SAME for both kernel shapes (and the one round 1's kernel used): 8 elements of a chunk in order,
+// then a shuffle tree over each group of 32 consecutive chunks, then a shuffle tree over the (at most 16) group sums — so a row
+// normalises to the same bits whether it is reached through a T = 1 step or inside a longer one.
+template <int LN_T, int LN_K>
+DEVI void ln_stats(const RowQ<LN_K>& x, int nk, int C, float* red, float& mean, float& rstd) {
+    constexpr int NW = LN_T / 32, NV = NW * LN_K;   // chunk j of warp w is "virtual warp" j * NW + w: chunks 32v .. 32v + 31
+    static_assert(NV <= 32, "one shuffle tree over the group sums");
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll
-        for (int e = 0; e < 8; e++) s += x.f[e];
-    }
-    const float mean = block_sum1(s, red) / (float)C;
-    float q = 0.f;
-    if (active) {
+    for (int j = 0; j < LN_K; j++) {
+        float s = 0.f;
+        if (j < nk) {
+            const H8 v = cvt8(x.q[j]);
 #pragma unroll
-        for (int e = 0; e < 8; e++) {
-            float d = x.f[e] - mean;
-            q += d * d;
+            for (int e = 0; e < 8; e++) s += v.f[e];
         }
+        s = warp_sum(s);
+        if (lane == 0) red[j * NW + warp] = s;
     }
-    const float var = block_sum1(q, red + 32) / (float)C;
-    const float rstd = 1.0f / sqrtf(var + 1e-5f);
-    const H8 ww = cvt8(wq), bb = cvt8(bq);
-    H8 o;
+    __syncthreads();
+    mean = warp_sum(lane < NV ? red[lane] : 0.f) / (float)C;
 #pragma unroll
-    for (int e = 0; e < 8; e++) o.f[e] = hr((x.f[e] - mean) * rstd * ww.f[e] + bb.f[e]);
-    return o;
+    for (int j = 0; j < LN_K; j++) {
+        float q = 0.f;
+        if (j < nk) {
+            const H8 v = cvt8(x.q[j]);
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+                const float d = v.f[e] - mean;
+                q += d * d;
+            }
+        }
+        q = warp_sum(q);
+        if (lane == 0) red[32 + j * NW + warp] = q;
+    }
+    __syncthreads();
+    rstd = 1.0f / sqrtf(warp_sum(lane < NV ? red[32 + lane] : 0.f) / (float)C + 1e-5f);
 }
 
-// One CTA per (sequence b, token t) row.  cur = LN(x[b,t]); prev = t ? LN(x[b,t-1]) : shift_state[b];
-// out_n = cur + (prev - cur) * mix_n.  The t == 0 CTA also owns the shift state of its sequence: it reads the old value and
-// afterwards stores LN(x[b,T-1]) — no other CTA touches that row, so there is no ordering hazard for T > 1.
-// Everything that the preceding kernels of the step do not produce — LN affine, the lerp coefficients and the shift-state row
-// (last written by this same kernel one step earlier) — is fetched BEFORE griddepcontrol.wait, so under programmatic dependent
-// launch only the x row load and two one-barrier reductions remain on the critical path.
-template <int NMIX>
-__global__ void __launch_bounds__(512, 2) ln_shift_mix_kernel(int T, int C, __half* __restrict__ x,
-                                                            const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
-                                                            __half* __restrict__ shift, long shift_stride,
-                                                            const int* __restrict__ slot_idx, MixPtrs<NMIX> mp,
-                                                            const float* __restrict__ part, int n_part, long part_stride) {
-    __shared__ float red[3 * 64];
+template <int NMIX, int LN_T, int LN_K>
+__global__ void __launch_bounds__(LN_T, LN_T == 128 ? 6 : 2) ln_shift_mix_kernel(int T, int C, int strip, __half* __restrict__ x,
+                                                              const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
+                                                              __half* __restrict__ shift, long shift_stride,
+                                                              const int* __restrict__ slot_idx, MixPtrs<NMIX> mp,
+                                                              const float* __restrict__ part, int n_part, long part_stride) {
+    __shared__ float red[4][64];
     pdl_launch_dependents();
-    const int m = blockIdx.x;
-    const int b = m / T, t = m - b * T;
-    const int c0 = threadIdx.x * 8;
-    const bool active = c0 < C;
-    __half* xrow = x + (size_t)m * C;
+    const int strips = (T + strip - 1) / strip;
+    const int b = blockIdx.x / strips, t0 = (blockIdx.x - b * strips) * strip;
+    const int t1 = min(T, t0 + strip);
+    const int tid = threadIdx.x;
+    const int nch = C >> 3;
+    int nk = 0;   // chunks of this thread: channels (j * LN_T + tid) * 8, j < nk
+#pragma unroll
+    for (int j = 0; j < LN_K; j++)
+        if (j * LN_T + tid < nch) nk = j + 1;
     __half* srow = shift + (size_t)(slot_idx ? slot_idx[b] : b) * shift_stride;
-    // kept packed (8 fp16 per int4) until used: 9 x 4 registers instead of 9 x 8
-    const int4 z4 = make_int4(0, 0, 0, 0);
-    // 64 registers per thread: two CTAs per SM, so the 256 rows of a decode step are ONE wave (and a CTA fits beside a GEMM CTA
-    // of the previous kernel under programmatic dependent launch).  The lerp coefficients are therefore fetched where they are
-    // used (L1/L2-resident: every CTA reads the same 6 x 8 KiB), not held across the LayerNorm.
-    int4 ww = z4, bb = z4, prevq = z4;
-    if (active) {
-        ww = *reinterpret_cast<const int4*>(ln_w + c0);
-        bb = *reinterpret_cast<const int4*>(ln_b + c0);
-        if (t == 0) prevq = *reinterpret_cast<const int4*>(srow + c0);
+    int4 prevq[LN_K];   // previous token's LN, packed fp16
+#pragma unroll
+    for (int j = 0; j < LN_K; j++) prevq[j] = make_int4(0, 0, 0, 0);
+    if (t0 == 0) {
+#pragma unroll
+        for (int j = 0; j < LN_K; j++)
+            if (j < nk) prevq[j] = *reinterpret_cast<const int4*>(srow + (j * LN_T + tid) * 8);
     }
     pdl_wait();
-    H8 prev = cvt8(prevq);
-    H8 xv;
+    int rb = 0;   // reduction buffer in use (a buffer comes round again after two more rows: every thread is long past it)
+
+    // LN of row m into packed fp16 (the affine parameters are re-read per row: 16 KiB, L1-resident, instead of 32 registers)
+    auto normalise = [&](const RowQ<LN_K>& xv, int4 (&outq)[LN_K]) {
+        float mean, rstd;
+        ln_stats<LN_T, LN_K>(xv, nk, C, red[rb], mean, rstd);
+        rb = (rb + 1) & 3;
 #pragma unroll
-    for (int e = 0; e < 8; e++) xv.f[e] = 0.f;
-    if (active) xv = ld8(xrow + c0);
-    if (part != nullptr && active) {
-        // The producing GEMM left its K split unreduced (glue.h, linear_f16_launch defer_splits): finish the residual add here,
-        // x <- fp16(x + fp16(p_0 + p_1 + ...)) in split order — bit for bit what the GEMM's own reduction stores — and write the
-        // row back for the residual stream.  T == 1 only (no CTA reads another CTA's row).
-        const float* pr = part + (size_t)m * C + c0;
-        float acc[8];
+        for (int j = 0; j < LN_K; j++)
+            if (j < nk) {
+                const int c0 = (j * LN_T + tid) * 8;
+                const H8 ww = cvt8(__ldg(reinterpret_cast<const int4*>(ln_w + c0))), bb = cvt8(__ldg(reinterpret_cast<const int4*>(ln_b + c0)));
+                const H8 v = cvt8(xv.q[j]);
+                __half* h = reinterpret_cast<__half*>(&outq[j]);
 #pragma unroll
-        for (int e = 0; e < 8; e++) acc[e] = 0.f;
+                for (int e = 0; e < 8; e++) h[e] = __float2half_rn((v.f[e] - mean) * rstd * ww.f[e] + bb.f[e]);
+            }
+    };
+    auto load_row = [&](const __half* row, RowQ<LN_K>& xv) {
+#pragma unroll
+        for (int j = 0; j < LN_K; j++)
+            if (j < nk) xv.q[j] = *reinterpret_cast<const int4*>(row + (j * LN_T + tid) * 8);
+    };
+
+    RowQ<LN_K> xv;
+    if (t0 > 0) {   // the strip's first token needs LN of the token before it (another strip's row: normalised once more here)
+        load_row(x + ((size_t)b * T + t0 - 1) * C, xv);
+        normalise(xv, prevq);
+    }
+    for (int t = t0; t < t1; t++) {
+        const size_t m = (size_t)b * T + t;
+        __half* xrow = x + m * C;
+        load_row(xrow, xv);
+        if (part != nullptr) {
+            // deferred K split of the producing GEMM (T == 1): x <- fp16(x + fp16(p_0 + p_1 + ...)) in split order, row written back
+#pragma unroll
+            for (int j = 0; j < LN_K; j++)
+                if (j < nk) {
+                    const int c0 = (j * LN_T + tid) * 8;
+                    const float* pr = part + m * C + c0;
+                    float acc[8];
+#pragma unroll
+                    for (int e = 0; e < 8; e++) acc[e] = 0.f;
 #pragma unroll 1
-        for (int z0 = 0; z0 < n_part; z0 += 2) {
-            float4 lo[2], hi[2];
+                    for (int z0 = 0; z0 < n_part; z0 += 2) {
+                        float4 lo[2], hi[2];
 #pragma unroll
-            for (int j = 0; j < 2; j++)
-                if (z0 + j < n_part) {
-                    const float4* q = reinterpret_cast<const float4*>(pr + (size_t)(z0 + j) * part_stride);
-                    lo[j] = __ldcg(q);
-                    hi[j] = __ldcg(q + 1);
-                }
+                        for (int u = 0; u < 2; u++)
+                            if (z0 + u < n_part) {
+                                const float4* q = reinterpret_cast<const float4*>(pr + (size_t)(z0 + u) * part_stride);
+                                lo[u] = __ldcg(q);
+                                hi[u] = __ldcg(q + 1);
+                            }
 #pragma unroll
-            for (int j = 0; j < 2; j++)
-                if (z0 + j < n_part) {
-                    acc[0] += lo[j].x; acc[1] += lo[j].y; acc[2] += lo[j].z; acc[3] += lo[j].w;
-                    acc[4] += hi[j].x; acc[5] += hi[j].y; acc[6] += hi[j].z; acc[7] += hi[j].w;
+                        for (int u = 0; u < 2; u++)
+                            if (z0 + u < n_part) {
+                                acc[0] += lo[u].x; acc[1] += lo[u].y; acc[2] += lo[u].z; acc[3] += lo[u].w;
+                                acc[4] += hi[u].x; acc[5] += hi[u].y; acc[6] += hi[u].z; acc[7] += hi[u].w;
+                            }
+                    }
+                    const H8 xin = cvt8(xv.q[j]);
+                    __half* h = reinterpret_cast<__half*>(&xv.q[j]);
+#pragma unroll
+                    for (int e = 0; e < 8; e++) h[e] = __float2half_rn(xin.f[e] + hr(acc[e]));
+                    *reinterpret_cast<int4*>(xrow + c0) = xv.q[j];
                 }
         }
+        int4 curq[LN_K];
+        normalise(xv, curq);
 #pragma unroll
-        for (int e = 0; e < 8; e++) xv.f[e] = hr(xv.f[e] + hr(acc[e]));
-        st8(xrow + c0, xv);
+        for (int j = 0; j < LN_K; j++)
+            if (j < nk) {
+                const int c0 = (j * LN_T + tid) * 8;
+                const H8 cur = cvt8(curq[j]), prev = cvt8(prevq[j]);
+                H8 dx;
+#pragma unroll
+                for (int e = 0; e < 8; e++) dx.f[e] = hr(prev.f[e] - cur.f[e]);
+#pragma unroll
+                for (int n = 0; n < NMIX; n++) {
+                    const H8 mv = cvt8(__ldg(reinterpret_cast<const int4*>(mp.mix[n] + c0)));
+                    H8 o;
+#pragma unroll
+                    for (int e = 0; e < 8; e++) o.f[e] = hr(cur.f[e] + hr(dx.f[e] * mv.f[e]));
+                    st8(mp.out[n] + m * C + c0, o);
+                }
+                prevq[j] = curq[j];
+            }
     }
-    const H8 cur = layer_norm8_pre(xv, active, C, ww, bb, red);
-    if (t > 0) {
-        H8 pv = xv;
-        if (active) pv = ld8(xrow - C + c0);
-        prev = layer_norm8_pre(pv, active, C, ww, bb, red + 64);
-    } else {
-        H8 last = cur;
-        if (T > 1) {
-            H8 lv = xv;
-            if (active) lv = ld8(xrow + (size_t)(T - 1) * C + c0);
-            last = layer_norm8_pre(lv, active, C, ww, bb, red + 64);
+    if (t0 == 0) {   // new shift state = LN(x[b, T-1])
+        if (t1 < T) {
+            load_row(x + ((size_t)b * T + T - 1) * C, xv);
+            normalise(xv, prevq);
         }
-        if (active) st8(srow + c0, last);
-    }
-    if (!active) return;
-    H8 dx;
 #pragma unroll
-    for (int e = 0; e < 8; e++) dx.f[e] = hr(prev.f[e] - cur.f[e]);
-#pragma unroll
-    for (int n = 0; n < NMIX; n++) {
-        const H8 mv = cvt8(__ldg(reinterpret_cast<const int4*>(mp.mix[n] + c0)));
-        H8 o;
-#pragma unroll
-        for (int e = 0; e < 8; e++) o.f[e] = hr(cur.f[e] + hr(dx.f[e] * mv.f[e]));
-        st8(mp.out[n] + (size_t)m * C + c0, o);
+        for (int j = 0; j < LN_K; j++)
+            if (j < nk) *reinterpret_cast<int4*>(srow + (j * LN_T + tid) * 8) = prevq[j];
     }
 }
 
@@ -357,8 +411,12 @@ int launch_ln_shift_mix6(int B, int T, int C, __half* x, const __half* ln_w, con
     if (B * T <= 0) return 0;
     if (C > 4096) return -4;  // B200_ERR_UNSUPPORTED: one thread per 8 channels, 512 threads (every RWKV-7 g1 size has C <= 4096)
     if (part && (T != 1 || n_part < 1)) return -1;
-    return launch_kernel(ln_shift_mix_kernel<6>, dim3(B * T), dim3(ln_threads(C)), 0, s, pdl, 0, T, C, x, ln_w, ln_b, shift,
-                         shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+    if (T == 1)
+        return launch_kernel(ln_shift_mix_kernel<6, 512, 1>, dim3(B), dim3(512), 0, s, pdl, 0, T, C, 1, x, ln_w, ln_b, shift,
+                             shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+    const int strip = T >= 8 ? 8 : T;
+    return launch_kernel(ln_shift_mix_kernel<6, 128, 4>, dim3(B * ((T + strip - 1) / strip)), dim3(128), 0, s, pdl, 0, T, C, strip, x,
+                         ln_w, ln_b, shift, shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
 }
 int launch_ln_shift_mix1(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
                          long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s, bool pdl, const float* part,
@@ -366,8 +424,12 @@ int launch_ln_shift_mix1(int B, int T, int C, __half* x, const __half* ln_w, con
     if (B * T <= 0) return 0;
     if (C > 4096) return -4;
     if (part && (T != 1 || n_part < 1)) return -1;
-    return launch_kernel(ln_shift_mix_kernel<1>, dim3(B * T), dim3(ln_threads(C)), 0, s, pdl, 0, T, C, x, ln_w, ln_b, shift,
-                         shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+    if (T == 1)
+        return launch_kernel(ln_shift_mix_kernel<1, 512, 1>, dim3(B), dim3(512), 0, s, pdl, 0, T, C, 1, x, ln_w, ln_b, shift,
+                             shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+    const int strip = T >= 8 ? 8 : T;
+    return launch_kernel(ln_shift_mix_kernel<1, 128, 4>, dim3(B * ((T + strip - 1) / strip)), dim3(128), 0, s, pdl, 0, T, C, strip, x,
+                         ln_w, ln_b, shift, shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
 }
 int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off, const __half* ln_w, const __half* ln_b,
                    __half* out, cudaStream_t s, bool pdl) {
