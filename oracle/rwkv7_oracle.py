@@ -333,12 +333,22 @@ def forward_batch(z, geom, tokens: List[List[int]], state, full_output=False, wk
 
 
 # ---- bsz-1 path ------------------------------------------------------------------------------------
-def forward_one(z, geom, token_or_x, state, wkv: str = "cpu", spmv: Optional[Callable] = None):
+def forward_one(z, geom, token_or_x, state, wkv: str = "cpu", spmv: Optional[Callable] = None, fast: bool = False):
     """``forward`` -> ``forward_one`` with ``RWKV_x070_TMix_one`` / ``RWKV_x070_CMix_one``
     (``Albatross/rwkv7.py:237-248``, ``:287-316``, ``:568-590``, ``:653-662``). Unbatched state layout."""
     C, H, N = geom.n_embd, geom.n_head, HEAD
     wkv_fn = _wkv_backend(wkv)
     spmv = spmv or (spmv_cpu if z["emb.weight"].device.type == "cpu" else spmv_ref_cuda)
+    if fast:   # same contract (fp32 accumulate, one rounding) through sgemm: measures the reference's GEMM-order noise (tests)
+        class _L:
+            linear = staticmethod(lambda a, W, bias=None: _linear(a, W, bias, True))
+            layer_norm, group_norm, normalize = F.layer_norm, F.group_norm, F.normalize
+        return _forward_one_impl(z, geom, token_or_x, state, wkv_fn, spmv, _L)
+    return _forward_one_impl(z, geom, token_or_x, state, wkv_fn, spmv, F)
+
+
+def _forward_one_impl(z, geom, token_or_x, state, wkv_fn, spmv, F):
+    C, H, N = geom.n_embd, geom.n_head, HEAD
     x = z["emb.weight"][token_or_x] if not torch.is_tensor(token_or_x) else token_or_x
     v_first = torch.empty_like(x)
     for i in range(geom.n_layer):

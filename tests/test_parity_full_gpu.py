@@ -189,27 +189,31 @@ def test_bsz1_forward_one_matches_oracle_forward_one(geom_name):
     with fp16 atomics in a run-dependent order."""
     geom, m, O, z, og = build_pair(geom_name, seed=45)
     toks = torch.randint(1, geom.vocab_size, (24,), generator=torch.Generator().manual_seed(3)).tolist()
-    st_a, st_b, st_c = m.generate_zero_state(0), O.zero_state(og, 0, "cuda"), O.zero_state(og, 0, "cuda")
+    st_a, st_b, st_c, st_d = m.generate_zero_state(0), O.zero_state(og, 0, "cuda"), O.zero_state(og, 0, "cuda"), O.zero_state(og, 0, "cuda")
     exact_spmv = lambda vec, mat: (vec.float() @ mat.float()).half()      # the same product with one rounding
-    worst_exact = worst_ref = worst_self = 0.0
+    w_exact = w_ref = n_spmv = n_gemm = 0.0
     for i, t in enumerate(toks):
         la = m.forward(t, st_a) if i % 2 else m.forward_one(t, st_a)
         lb = O.forward_one(z, og, t, st_b, wkv="ref_cuda")                 # the reference's own sparse kernel (fp16 atomics)
         lc = O.forward_one(z, og, t, st_c, wkv="ref_cuda", spmv=exact_spmv)
+        ld = O.forward_one(z, og, t, st_d, wkv="ref_cuda", spmv=exact_spmv, fast=True)   # + GEMMs through fp32 sgemm
         assert la.shape == (geom.vocab_size,)
         assert int(la.float().argmax()) == int(lb.float().argmax()) == int(lc.float().argmax()), f"bsz-1 greedy token differs at step {i}"
-        worst_exact, worst_ref, worst_self = max(worst_exact, rel(la, lc)), max(worst_ref, rel(la, lb)), max(worst_self, rel(lc, lb))
+        w_exact, w_ref = max(w_exact, rel(la, lc)), max(w_ref, rel(la, lb))
+        n_spmv, n_gemm = max(n_spmv, rel(lc, lb)), max(n_gemm, rel(ld, lc))
     assert int(st_a[2]) == len(toks) == int(st_b[2])
-    s1_exact, s1_ref, s1_self = rel_l2(st_a[1], st_c[1]), rel_l2(st_a[1], st_b[1]), rel_l2(st_c[1], st_b[1])
-    # The reference's sparse product accumulates in fp16 (hfma2 per 64-row slab, fp16 atomicAdd across slabs in a run-dependent
-    # order, .cu:296-309): at 1.5B its logits move by 1.4e-2 ... 4.5e-2 from run to run of this very test.  The parity bar is
-    # therefore asserted against the reference MATH with an exactly rounded product (deterministic); the distance to the
-    # reference's own kernel is recorded next to that kernel's distance to the same exact evaluation, with a sanity bound only.
-    record(f"bsz1_forward_one_{geom_name}", steps=len(toks), logits_rel_vs_exact_product_oracle=worst_exact,
-           logits_rel_vs_reference_kernel_oracle=worst_ref, logits_rel_reference_kernel_vs_exact=worst_self,
-           state1_rel_l2_vs_exact=s1_exact, state1_rel_l2_vs_reference_kernel=s1_ref, state1_rel_l2_reference_kernel_vs_exact=s1_self)
-    assert worst_exact <= LOGIT_TOL and s1_exact <= 3 * STATE_TOL
-    assert worst_ref <= 0.1 and s1_ref <= 0.02
+    s_exact, s_ref = rel_l2(st_a[1], st_c[1]), rel_l2(st_a[1], st_b[1])
+    sn_spmv, sn_gemm = rel_l2(st_c[1], st_b[1]), rel_l2(st_d[1], st_c[1])
+    # Two noise sources of the reference on this path, both measured here: its sparse product accumulates in fp16 (hfma2 per
+    # 64-row slab, fp16 atomicAdd across slabs in a run-dependent order, .cu:296-309: 1e-2 ... 4.5e-2 on the 1.5B logits from run
+    # to run of this test), and its M = 1 GEMMs (cuBLAS gemv / split-K with reduced-precision fp16 reductions) against the same
+    # math through fp32 sgemm.  The bar is north_star's where the reference meets it against itself, else 1.5x its own noise.
+    record(f"bsz1_forward_one_{geom_name}", steps=len(toks), logits_rel_vs_exact_product_oracle=w_exact,
+           logits_rel_vs_reference_kernel_oracle=w_ref, reference_noise_sparse_kernel=n_spmv, reference_noise_gemm_order=n_gemm,
+           state1_rel_l2_vs_exact=s_exact, state1_rel_l2_vs_reference_kernel=s_ref, state1_reference_noise_sparse_kernel=sn_spmv,
+           state1_reference_noise_gemm_order=sn_gemm)
+    assert w_exact <= bound(LOGIT_TOL, n_gemm) and s_exact <= bound(3 * STATE_TOL, sn_gemm)
+    assert w_ref <= bound(LOGIT_TOL, n_gemm + n_spmv) + LOGIT_TOL and s_ref <= bound(3 * STATE_TOL, sn_gemm + sn_spmv) + 3 * STATE_TOL
 
 
 @needs_ref
