@@ -295,3 +295,39 @@ def test_batched_slot_migration_equals_slot_by_slot():
     for s_, d_ in zip(src, dst):
         assert torch.equal(b1[1][:, d_].cpu(), a[1][:, s_].cpu()) and int(b1[2][d_]) == int(a[2][s_])
     assert torch.count_nonzero(b1[1][:, 0]) == 0 and torch.count_nonzero(b1[0][:, :, 2]) == 0        # other slots untouched
+
+
+def test_process_per_gpu_engine_matches_isolated_greedy():
+    """MPEngineCore (one worker PROCESS per GPU behind the AsyncEngineCore API): the worker builds the seeded synthetic model on
+    its own GPU; every request's tokens equal an isolated greedy run of the same model in this process; stop tokens end a request
+    without being delivered; both workers of a 2-GPU box take work."""
+    from chirrup_b200.engine import FinishReason, ModelLoadConfig
+    from chirrup_b200.engine_mp import MPEngineCore
+    from chirrup_b200.rwkv7 import RWKV_x070, make_args
+
+    geom = GEOMETRIES["small"]
+    syn = {"geom": "small", "seed": 8, "recipe": "trained_like"}
+    m_ref = RWKV_x070(make_args(), state_dict=make_checkpoint(geom, seed=8, recipe="trained_like", device="cuda", dtype=torch.float16))
+    g = torch.Generator().manual_seed(2)
+    prompts = [torch.randint(1, geom.vocab_size, (n,), generator=g).tolist() for n in (1, 5, 12, 47, 130, 3, 64, 9)]
+    n_workers = min(2, torch.cuda.device_count())
+
+    async def main():
+        eng = MPEngineCore()
+        await eng.init(n_workers, ModelLoadConfig(vocab_size=geom.vocab_size, synthetic=syn), batch_size=4, load_timeout_s=300)
+        kw = dict(top_k=1, max_tokens=9, stop_tokens=[], presence_penalty=0.0, frequency_penalty=0.0)
+        comps = [eng.completion(prefill_tokens=p, **kw) for p in prompts]
+        outs = await asyncio.gather(*[c.get_full_completion() for c in comps])
+        streamed = [ev[1] async for ev in eng.completion(prefill_tokens=prompts[3], **kw)]        # per-token iteration form
+        want = _greedy_alone(m_ref, prompts[2], 9)
+        stopper = eng.completion(prefill_tokens=prompts[2], **dict(kw, stop_tokens=[want[4]]))
+        stopped = await stopper.get_full_completion()
+        eng.shutdown()
+        return outs, streamed, stopped, stopper.finish_reason, want, eng.worker_steps
+
+    outs, streamed, stopped, reason, want, steps = asyncio.run(main())
+    for p, o in zip(prompts, outs):
+        assert o == _greedy_alone(m_ref, p, 9), f"prompt len {len(p)}"
+    assert streamed == outs[3]
+    assert stopped == want[:want.index(want[4])] and reason == FinishReason.STOP
+    assert len(steps) == n_workers and all(v["decode_tokens"] > 0 for v in steps.values())
