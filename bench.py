@@ -2,16 +2,20 @@
 """Benchmark of the hot path: RWKV-7 batched decode step (BASELINE.json metric
 "RWKV-7 7.2B decode tok/s/GPU @bsz256; WKV step HBM GB/s vs peak").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--geom 7.2B] [--bsz 256]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config decode|prefill|engine|migration]
+                    [--geom 7.2B] [--bsz 256]
 
-One "step" = one decode forward (T = 1) of `bsz` sequences per GPU through every layer + head + greedy sampling.
-N > 1: launched by torchrun, one replica per GPU, requests sharded by rank, no data-path collective ("weak" scaling); NCCL is
-used only for the barrier and the max-over-ranks of the device time.
-
+--config decode (default, BASELINE configs[2]): one "step" = one decode forward (T = 1) of `bsz` sequences per GPU through every
+layer + head + greedy sampling.  N > 1: launched by torchrun, one replica per GPU, requests sharded by rank, no data-path
+collective ("weak" scaling); NCCL is used only for the barrier and the max-over-ranks of the device time.
 Printed JSON keys (contract in the task statement): value = whole-job tok/s with inputs resident in HBM (CUDA-graph replay of
-the step, CUDA events); e2e = the same through the public Python API with HOST token buffers (pinned H2D of token ids, D2H
-of the sampled ids, every step); roofline = the WKV kernel against measured HBM peak; cpu_baseline = the CPU oracle
-(the reference's PyTorch CPU path, oracle/rwkv7_oracle.py) on a bounded sample of the same workload.
+the step, CUDA events); e2e = the same through the public Python API with HOST token lists (List[List[int]] as Chirrup's worker
+passes them: H2D inside the API, D2H of the sampled ids, host-synchronised every step); roofline = the fused WKV kernel against
+the measured HBM peak, alone and inside the step; roofline_gemm = the rest of the step against the tensor peak; engine = the
+same configuration through the continuous-batching engine (one worker process per GPU, one task queue); cpu_baseline = the
+reference's own model code on the host cores (a child process running the reference arm, one full-depth step).
+--config prefill / engine / migration: BASELINE configs[3], configs[2] through the worker loop only, configs[4] (2 GPUs).
+--impl reference: the reference's own Albatross/rwkv7.py on the host cores (oracle/ref_cpu.py), this arm's configuration.
 """
 from __future__ import annotations
 
