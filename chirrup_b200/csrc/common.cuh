@@ -164,6 +164,13 @@ DEVI float rcp_approx_ftz(float x) {
 DEVI void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 DEVI void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// 16-byte asynchronous global -> shared copy (LDGSTS): the next chunk's inputs travel while this chunk computes
+DEVI void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+DEVI void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+DEVI void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 DEVI float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -162,6 +162,9 @@ __global__ void __launch_bounds__(LN_T, LN_T == 128 ? 6 : 2) ln_shift_mix_kernel
                                                               const int* __restrict__ slot_idx, MixPtrs<NMIX> mp,
                                                               const float* __restrict__ part, int n_part, long part_stride) {
     __shared__ float red[4][64];
+    // decode shape only: this thread's 16 bytes of ln_w, ln_b and of every lerp coefficient, fetched by cp.async BEFORE
+    // griddepcontrol.wait (they are weights) so that no L2 round trip for them is left on the row's critical path
+    extern __shared__ __align__(16) int4 coef[];   // [(2 + NMIX)][LN_T], LN_K == 1 only
     pdl_launch_dependents();
     const int strips = (T + strip - 1) / strip;
     const int b = blockIdx.x / strips, t0 = (blockIdx.x - b * strips) * strip;
@@ -181,6 +184,13 @@ __global__ void __launch_bounds__(LN_T, LN_T == 128 ? 6 : 2) ln_shift_mix_kernel
         for (int j = 0; j < LN_K; j++)
             if (j < nk) prevq[j] = *reinterpret_cast<const int4*>(srow + (j * LN_T + tid) * 8);
     }
+    if (LN_K == 1 && nk == 1) {
+        cp_async16(&coef[0 * LN_T + tid], ln_w + tid * 8);
+        cp_async16(&coef[1 * LN_T + tid], ln_b + tid * 8);
+#pragma unroll
+        for (int n = 0; n < NMIX; n++) cp_async16(&coef[(2 + n) * LN_T + tid], mp.mix[n] + tid * 8);
+        cp_async_commit();
+    }
     pdl_wait();
     int rb = 0;   // reduction buffer in use (a buffer comes round again after two more rows: every thread is long past it)
 
@@ -193,7 +203,9 @@ __global__ void __launch_bounds__(LN_T, LN_T == 128 ? 6 : 2) ln_shift_mix_kernel
         for (int j = 0; j < LN_K; j++)
             if (j < nk) {
                 const int c0 = (j * LN_T + tid) * 8;
-                const H8 ww = cvt8(__ldg(reinterpret_cast<const int4*>(ln_w + c0))), bb = cvt8(__ldg(reinterpret_cast<const int4*>(ln_b + c0)));
+                if (LN_K == 1) cp_async_wait_all();
+                const H8 ww = cvt8(LN_K == 1 ? coef[tid] : __ldg(reinterpret_cast<const int4*>(ln_w + c0)));
+                const H8 bb = cvt8(LN_K == 1 ? coef[LN_T + tid] : __ldg(reinterpret_cast<const int4*>(ln_b + c0)));
                 const H8 v = cvt8(xv.q[j]);
                 __half* h = reinterpret_cast<__half*>(&outq[j]);
 #pragma unroll
@@ -226,17 +238,17 @@ __global__ void __launch_bounds__(LN_T, LN_T == 128 ? 6 : 2) ln_shift_mix_kernel
 #pragma unroll
                     for (int e = 0; e < 8; e++) acc[e] = 0.f;
 #pragma unroll 1
-                    for (int z0 = 0; z0 < n_part; z0 += 2) {
-                        float4 lo[2], hi[2];
+                    for (int z0 = 0; z0 < n_part; z0 += 4) {   // up to four splits (all there are, in practice) in ONE round trip
+                        float4 lo[4], hi[4];
 #pragma unroll
-                        for (int u = 0; u < 2; u++)
+                        for (int u = 0; u < 4; u++)
                             if (z0 + u < n_part) {
                                 const float4* q = reinterpret_cast<const float4*>(pr + (size_t)(z0 + u) * part_stride);
                                 lo[u] = __ldcg(q);
                                 hi[u] = __ldcg(q + 1);
                             }
 #pragma unroll
-                        for (int u = 0; u < 2; u++)
+                        for (int u = 0; u < 4; u++)
                             if (z0 + u < n_part) {
                                 acc[0] += lo[u].x; acc[1] += lo[u].y; acc[2] += lo[u].z; acc[3] += lo[u].w;
                                 acc[4] += hi[u].x; acc[5] += hi[u].y; acc[6] += hi[u].z; acc[7] += hi[u].w;
@@ -261,7 +273,7 @@ __global__ void __launch_bounds__(LN_T, LN_T == 128 ? 6 : 2) ln_shift_mix_kernel
                 for (int e = 0; e < 8; e++) dx.f[e] = hr(prev.f[e] - cur.f[e]);
 #pragma unroll
                 for (int n = 0; n < NMIX; n++) {
-                    const H8 mv = cvt8(__ldg(reinterpret_cast<const int4*>(mp.mix[n] + c0)));
+                    const H8 mv = cvt8(LN_K == 1 ? coef[(2 + n) * LN_T + tid] : __ldg(reinterpret_cast<const int4*>(mp.mix[n] + c0)));
                     H8 o;
 #pragma unroll
                     for (int e = 0; e < 8; e++) o.f[e] = hr(cur.f[e] + hr(dx.f[e] * mv.f[e]));
@@ -411,9 +423,19 @@ int launch_ln_shift_mix6(int B, int T, int C, __half* x, const __half* ln_w, con
     if (B * T <= 0) return 0;
     if (C > 4096) return -4;  // B200_ERR_UNSUPPORTED: one thread per 8 channels, 512 threads (every RWKV-7 g1 size has C <= 4096)
     if (part && (T != 1 || n_part < 1)) return -1;
-    if (T == 1)
-        return launch_kernel(ln_shift_mix_kernel<6, 512, 1>, dim3(B), dim3(512), 0, s, pdl, 0, T, C, 1, x, ln_w, ln_b, shift,
+    if (T == 1) {
+        const size_t coef_bytes = (size_t)(2 + 6) * 512 * 16;
+        static bool attr_done[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(ln_shift_mix_kernel<6, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)coef_bytes);
+            if (e != cudaSuccess) return (int)e;
+            if (dev >= 0 && dev < 64) attr_done[dev] = true;
+        }
+        return launch_kernel(ln_shift_mix_kernel<6, 512, 1>, dim3(B), dim3(512), coef_bytes, s, pdl, 0, T, C, 1, x, ln_w, ln_b, shift,
                              shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+    }
     const int strip = T >= 8 ? 8 : T;
     return launch_kernel(ln_shift_mix_kernel<6, 128, 4>, dim3(B * ((T + strip - 1) / strip)), dim3(128), 0, s, pdl, 0, T, C, strip, x,
                          ln_w, ln_b, shift, shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
@@ -424,9 +446,19 @@ int launch_ln_shift_mix1(int B, int T, int C, __half* x, const __half* ln_w, con
     if (B * T <= 0) return 0;
     if (C > 4096) return -4;
     if (part && (T != 1 || n_part < 1)) return -1;
-    if (T == 1)
-        return launch_kernel(ln_shift_mix_kernel<1, 512, 1>, dim3(B), dim3(512), 0, s, pdl, 0, T, C, 1, x, ln_w, ln_b, shift,
+    if (T == 1) {
+        const size_t coef_bytes = (size_t)(2 + 1) * 512 * 16;
+        static bool attr_done[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(ln_shift_mix_kernel<1, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)coef_bytes);
+            if (e != cudaSuccess) return (int)e;
+            if (dev >= 0 && dev < 64) attr_done[dev] = true;
+        }
+        return launch_kernel(ln_shift_mix_kernel<1, 512, 1>, dim3(B), dim3(512), coef_bytes, s, pdl, 0, T, C, 1, x, ln_w, ln_b, shift,
                              shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+    }
     const int strip = T >= 8 ? 8 : T;
     return launch_kernel(ln_shift_mix_kernel<1, 128, 4>, dim3(B * ((T + strip - 1) / strip)), dim3(128), 0, s, pdl, 0, T, C, strip, x,
                          ln_w, ln_b, shift, shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);

@@ -64,13 +64,6 @@ DEVI uint32_t pack2(float lo, float hi) {
     __half2 h = __floats2half2_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&h);
 }
-// 16-byte asynchronous global -> shared copy (LDGSTS): the next chunk's inputs travel while this chunk computes
-DEVI void cp_async16(void* smem_dst, const void* gmem_src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
-}
-DEVI void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-DEVI void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-
 DEVI uint32_t lds32(const __half* p) { return *reinterpret_cast<const uint32_t*>(p); }
 // four 8x8 b16 matrices, TRANSPOSED on the way in: lane l supplies the address of row (l & 7) of matrix (l >> 3); thread
 // (g, tq) receives elements (row 2tq, 2tq+1; column g) of each — the mma fragment of an operand stored k-major
