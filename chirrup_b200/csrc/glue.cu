@@ -111,40 +111,39 @@ __global__ void embed_gather_kernel(int M, int C, int V, const int* __restrict__
 // step (T = 1: 256 rows, at most two CTAs per SM whatever their size) keeps round 1's 512 threads x one chunk, where the row's
 // latency, not the number of rows in flight, is what counts.
 template <int LN_K>
-struct RowQ {   // one row's share of this thread, packed fp16 (converted where it is used)
-    int4 q[LN_K];
+struct RowF {   // one row's share of this thread in fp32: chunk j = channels (j * LN_T + tid) * 8 .. + 7
+    float f[LN_K][8];
 };
 
-// fp32 two-pass statistics (as ATen) of a row spread over the CTA; `red` = 2 x 16 floats not used by the previous two calls.
-// The summation tree is the SAME for both kernel shapes (and the one round 1's kernel used): 8 elements of a chunk in order,
-// then a shuffle tree over each group of 32 consecutive chunks, then a shuffle tree over the (at most 16) group sums — so a row
-// normalises to the same bits whether it is reached through a T = 1 step or inside a longer one.
-template <int LN_T, int LN_K>
-DEVI void ln_stats(const RowQ<LN_K>& x, int nk, int C, float* red, float& mean, float& rstd) {
+// fp32 two-pass statistics (as ATen) of a row spread over the CTA; `red` = 2 x 32 floats not used by the previous two calls.
+// On return v holds x - mean.  The summation tree is the SAME for both kernel shapes (and the one round 1's kernel used):
+// 8 elements of a chunk in order, then a shuffle tree over each group of 32 consecutive chunks, then a shuffle tree over the
+// (at most 16) group sums — so a row normalises to the same bits whether it is reached through a T = 1 step or a longer one.
+template <int LN_T, int LN_K, bool FULL>
+DEVI void ln_stats(RowF<LN_K>& v, int nk, int C, float* red, float& rstd) {
     constexpr int NW = LN_T / 32, NV = NW * LN_K;   // chunk j of warp w is "virtual warp" j * NW + w: chunks 32v .. 32v + 31
     static_assert(NV <= 32, "one shuffle tree over the group sums");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll
     for (int j = 0; j < LN_K; j++) {
         float s = 0.f;
-        if (j < nk) {
-            const H8 v = cvt8(x.q[j]);
+        if (FULL || j < nk) {
 #pragma unroll
-            for (int e = 0; e < 8; e++) s += v.f[e];
+            for (int e = 0; e < 8; e++) s += v.f[j][e];
         }
         s = warp_sum(s);
         if (lane == 0) red[j * NW + warp] = s;
     }
     __syncthreads();
-    mean = warp_sum(lane < NV ? red[lane] : 0.f) / (float)C;
+    const float mean = warp_sum(lane < NV ? red[lane] : 0.f) / (float)C;
 #pragma unroll
     for (int j = 0; j < LN_K; j++) {
         float q = 0.f;
-        if (j < nk) {
-            const H8 v = cvt8(x.q[j]);
+        if (FULL || j < nk) {
 #pragma unroll
             for (int e = 0; e < 8; e++) {
-                const float d = v.f[e] - mean;
+                const float d = v.f[j][e] - mean;
+                v.f[j][e] = d;
                 q += d * d;
             }
         }
@@ -155,13 +154,21 @@ DEVI void ln_stats(const RowQ<LN_K>& x, int nk, int C, float* red, float& mean, 
     rstd = 1.0f / sqrtf(warp_sum(lane < NV ? red[32 + lane] : 0.f) / (float)C + 1e-5f);
 }
 
-template <int NMIX, int LN_T, int LN_K>
+// FULL: C == LN_T * LN_K * 8, every thread owns LN_K whole chunks (no per-chunk predicate; C = 4096 in both shapes).
+// The elementwise half ops after the LayerNorm (prev - cur, * mix, + cur: each an ATen fp16 op = fp32 op + one rounding) run
+// as HSUB2 / HMUL2 / HADD2 with contraction disabled (__h*2_rn): for +, -, x of two fp16 values the fp32 intermediate is
+// exact or rounds innocuously (24 >= 2 * 11 + 2 bits), so the packed op returns the same bits at a quarter of the
+// instructions — the prefill shape of this kernel was issue-bound (57 % issue-active, 2.8 TB/s), not DRAM-bound.
+template <int NMIX, int LN_T, int LN_K, bool FULL>
 __global__ void __launch_bounds__(LN_T, LN_T == 128 ? 6 : 2) ln_shift_mix_kernel(int T, int C, int strip, __half* __restrict__ x,
                                                               const __half* __restrict__ ln_w, const __half* __restrict__ ln_b,
                                                               __half* __restrict__ shift, long shift_stride,
                                                               const int* __restrict__ slot_idx, MixPtrs<NMIX> mp,
                                                               const float* __restrict__ part, int n_part, long part_stride) {
     __shared__ float red[4][64];
+    // prefill shape: this thread's LN affine parameters as fp32, [chunk j][w lo, w hi, b lo, b hi][tid] — thread-private
+    // (written and read by the same thread, so no barrier), converted once per CTA instead of once per row
+    __shared__ float4 lnc[LN_K > 1 ? 4 * LN_K * LN_T : 1];
     // decode shape only: this thread's 16 bytes of ln_w, ln_b and of every lerp coefficient, fetched by cp.async BEFORE
     // griddepcontrol.wait (they are weights) so that no L2 round trip for them is left on the row's critical path
     extern __shared__ __align__(16) int4 coef[];   // [(2 + NMIX)][LN_T], LN_K == 1 only
@@ -182,114 +189,148 @@ __global__ void __launch_bounds__(LN_T, LN_T == 128 ? 6 : 2) ln_shift_mix_kernel
     if (t0 == 0) {
 #pragma unroll
         for (int j = 0; j < LN_K; j++)
-            if (j < nk) prevq[j] = *reinterpret_cast<const int4*>(srow + (j * LN_T + tid) * 8);
+            if (FULL || j < nk) prevq[j] = *reinterpret_cast<const int4*>(srow + (j * LN_T + tid) * 8);
     }
-    if (LN_K == 1 && nk == 1) {
-        cp_async16(&coef[0 * LN_T + tid], ln_w + tid * 8);
-        cp_async16(&coef[1 * LN_T + tid], ln_b + tid * 8);
+    if (LN_K == 1) {
+        if (nk == 1) {
+            cp_async16(&coef[0 * LN_T + tid], ln_w + tid * 8);
+            cp_async16(&coef[1 * LN_T + tid], ln_b + tid * 8);
 #pragma unroll
-        for (int n = 0; n < NMIX; n++) cp_async16(&coef[(2 + n) * LN_T + tid], mp.mix[n] + tid * 8);
-        cp_async_commit();
+            for (int n = 0; n < NMIX; n++) cp_async16(&coef[(2 + n) * LN_T + tid], mp.mix[n] + tid * 8);
+            cp_async_commit();
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < LN_K; j++)
+            if (FULL || j < nk) {
+                const int c0 = (j * LN_T + tid) * 8;
+                const H8 ww = cvt8(__ldg(reinterpret_cast<const int4*>(ln_w + c0))), bb = cvt8(__ldg(reinterpret_cast<const int4*>(ln_b + c0)));
+                lnc[(j * 4 + 0) * LN_T + tid] = make_float4(ww.f[0], ww.f[1], ww.f[2], ww.f[3]);
+                lnc[(j * 4 + 1) * LN_T + tid] = make_float4(ww.f[4], ww.f[5], ww.f[6], ww.f[7]);
+                lnc[(j * 4 + 2) * LN_T + tid] = make_float4(bb.f[0], bb.f[1], bb.f[2], bb.f[3]);
+                lnc[(j * 4 + 3) * LN_T + tid] = make_float4(bb.f[4], bb.f[5], bb.f[6], bb.f[7]);
+            }
     }
     pdl_wait();
     int rb = 0;   // reduction buffer in use (a buffer comes round again after two more rows: every thread is long past it)
 
-    // LN of row m into packed fp16 (the affine parameters are re-read per row: 16 KiB, L1-resident, instead of 32 registers)
-    auto normalise = [&](const RowQ<LN_K>& xv, int4 (&outq)[LN_K]) {
-        float mean, rstd;
-        ln_stats<LN_T, LN_K>(xv, nk, C, red[rb], mean, rstd);
+    // LN of the row in v (fp32) into packed fp16
+    auto normalise = [&](RowF<LN_K>& v, int4 (&outq)[LN_K]) {
+        float rstd;
+        ln_stats<LN_T, LN_K, FULL>(v, nk, C, red[rb], rstd);
         rb = (rb + 1) & 3;
 #pragma unroll
         for (int j = 0; j < LN_K; j++)
-            if (j < nk) {
-                const int c0 = (j * LN_T + tid) * 8;
-                if (LN_K == 1) cp_async_wait_all();
-                const H8 ww = cvt8(LN_K == 1 ? coef[tid] : __ldg(reinterpret_cast<const int4*>(ln_w + c0)));
-                const H8 bb = cvt8(LN_K == 1 ? coef[LN_T + tid] : __ldg(reinterpret_cast<const int4*>(ln_b + c0)));
-                const H8 v = cvt8(xv.q[j]);
-                __half* h = reinterpret_cast<__half*>(&outq[j]);
+            if (FULL || j < nk) {
+                float w[8], bb[8];
+                if (LN_K == 1) {
+                    cp_async_wait_all();
+                    const H8 w8 = cvt8(coef[tid]), b8 = cvt8(coef[LN_T + tid]);
 #pragma unroll
-                for (int e = 0; e < 8; e++) h[e] = __float2half_rn((v.f[e] - mean) * rstd * ww.f[e] + bb.f[e]);
+                    for (int e = 0; e < 8; e++) w[e] = w8.f[e], bb[e] = b8.f[e];
+                } else {
+                    const float4 w0 = lnc[(j * 4 + 0) * LN_T + tid], w1 = lnc[(j * 4 + 1) * LN_T + tid];
+                    const float4 b0 = lnc[(j * 4 + 2) * LN_T + tid], b1 = lnc[(j * 4 + 3) * LN_T + tid];
+                    w[0] = w0.x, w[1] = w0.y, w[2] = w0.z, w[3] = w0.w, w[4] = w1.x, w[5] = w1.y, w[6] = w1.z, w[7] = w1.w;
+                    bb[0] = b0.x, bb[1] = b0.y, bb[2] = b0.z, bb[3] = b0.w, bb[4] = b1.x, bb[5] = b1.y, bb[6] = b1.z, bb[7] = b1.w;
+                }
+                __half2* h2 = reinterpret_cast<__half2*>(&outq[j]);
+#pragma unroll
+                for (int e = 0; e < 4; e++)
+                    h2[e] = __floats2half2_rn(v.f[j][2 * e] * rstd * w[2 * e] + bb[2 * e],
+                                              v.f[j][2 * e + 1] * rstd * w[2 * e + 1] + bb[2 * e + 1]);
             }
     };
-    auto load_row = [&](const __half* row, RowQ<LN_K>& xv) {
+    auto load_row = [&](const __half* row, RowF<LN_K>& v) {
+        int4 q[LN_K];
 #pragma unroll
         for (int j = 0; j < LN_K; j++)
-            if (j < nk) xv.q[j] = *reinterpret_cast<const int4*>(row + (j * LN_T + tid) * 8);
+            if (FULL || j < nk) q[j] = *reinterpret_cast<const int4*>(row + (j * LN_T + tid) * 8);
+#pragma unroll
+        for (int j = 0; j < LN_K; j++)
+            if (FULL || j < nk) {
+                const H8 h = cvt8(q[j]);
+#pragma unroll
+                for (int e = 0; e < 8; e++) v.f[j][e] = h.f[e];
+            }
     };
 
-    RowQ<LN_K> xv;
+    RowF<LN_K> v;
     if (t0 > 0) {   // the strip's first token needs LN of the token before it (another strip's row: normalised once more here)
-        load_row(x + ((size_t)b * T + t0 - 1) * C, xv);
-        normalise(xv, prevq);
+        load_row(x + ((size_t)b * T + t0 - 1) * C, v);
+        normalise(v, prevq);
     }
     for (int t = t0; t < t1; t++) {
         const size_t m = (size_t)b * T + t;
         __half* xrow = x + m * C;
-        load_row(xrow, xv);
-        if (part != nullptr) {
-            // deferred K split of the producing GEMM (T == 1): x <- fp16(x + fp16(p_0 + p_1 + ...)) in split order, row written back
+        load_row(xrow, v);
+        if (LN_K == 1 && part != nullptr && nk == 1) {
+            // deferred K split of the producing GEMM (T == 1, decode shape): x <- fp16(x + fp16(p_0 + p_1 + ...)) in split
+            // order, row written back
+            const int c0 = tid * 8;
+            const float* pr = part + m * C + c0;
+            float acc[8];
 #pragma unroll
-            for (int j = 0; j < LN_K; j++)
-                if (j < nk) {
-                    const int c0 = (j * LN_T + tid) * 8;
-                    const float* pr = part + m * C + c0;
-                    float acc[8];
-#pragma unroll
-                    for (int e = 0; e < 8; e++) acc[e] = 0.f;
+            for (int e = 0; e < 8; e++) acc[e] = 0.f;
 #pragma unroll 1
-                    for (int z0 = 0; z0 < n_part; z0 += 4) {   // up to four splits (all there are, in practice) in ONE round trip
-                        float4 lo[4], hi[4];
+            for (int z0 = 0; z0 < n_part; z0 += 4) {   // up to four splits (all there are, in practice) in ONE round trip
+                float4 lo[4], hi[4];
 #pragma unroll
-                        for (int u = 0; u < 4; u++)
-                            if (z0 + u < n_part) {
-                                const float4* q = reinterpret_cast<const float4*>(pr + (size_t)(z0 + u) * part_stride);
-                                lo[u] = __ldcg(q);
-                                hi[u] = __ldcg(q + 1);
-                            }
-#pragma unroll
-                        for (int u = 0; u < 4; u++)
-                            if (z0 + u < n_part) {
-                                acc[0] += lo[u].x; acc[1] += lo[u].y; acc[2] += lo[u].z; acc[3] += lo[u].w;
-                                acc[4] += hi[u].x; acc[5] += hi[u].y; acc[6] += hi[u].z; acc[7] += hi[u].w;
-                            }
+                for (int u = 0; u < 4; u++)
+                    if (z0 + u < n_part) {
+                        const float4* q = reinterpret_cast<const float4*>(pr + (size_t)(z0 + u) * part_stride);
+                        lo[u] = __ldcg(q);
+                        hi[u] = __ldcg(q + 1);
                     }
-                    const H8 xin = cvt8(xv.q[j]);
-                    __half* h = reinterpret_cast<__half*>(&xv.q[j]);
 #pragma unroll
-                    for (int e = 0; e < 8; e++) h[e] = __float2half_rn(xin.f[e] + hr(acc[e]));
-                    *reinterpret_cast<int4*>(xrow + c0) = xv.q[j];
-                }
+                for (int u = 0; u < 4; u++)
+                    if (z0 + u < n_part) {
+                        acc[0] += lo[u].x; acc[1] += lo[u].y; acc[2] += lo[u].z; acc[3] += lo[u].w;
+                        acc[4] += hi[u].x; acc[5] += hi[u].y; acc[6] += hi[u].z; acc[7] += hi[u].w;
+                    }
+            }
+            int4 xq;
+            __half2* h2 = reinterpret_cast<__half2*>(&xq);
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                h2[e] = __floats2half2_rn(v.f[0][2 * e] + hr(acc[2 * e]), v.f[0][2 * e + 1] + hr(acc[2 * e + 1]));
+                const float2 r = __half22float2(h2[e]);
+                v.f[0][2 * e] = r.x, v.f[0][2 * e + 1] = r.y;
+            }
+            *reinterpret_cast<int4*>(xrow + c0) = xq;
         }
         int4 curq[LN_K];
-        normalise(xv, curq);
+        normalise(v, curq);
 #pragma unroll
         for (int j = 0; j < LN_K; j++)
-            if (j < nk) {
+            if (FULL || j < nk) {
                 const int c0 = (j * LN_T + tid) * 8;
-                const H8 cur = cvt8(curq[j]), prev = cvt8(prevq[j]);
-                H8 dx;
+                const __half2* c2 = reinterpret_cast<const __half2*>(&curq[j]);
+                const __half2* p2 = reinterpret_cast<const __half2*>(&prevq[j]);
+                __half2 dx[4];
 #pragma unroll
-                for (int e = 0; e < 8; e++) dx.f[e] = hr(prev.f[e] - cur.f[e]);
+                for (int e = 0; e < 4; e++) dx[e] = __hsub2_rn(p2[e], c2[e]);
 #pragma unroll
                 for (int n = 0; n < NMIX; n++) {
-                    const H8 mv = cvt8(LN_K == 1 ? coef[(2 + n) * LN_T + tid] : __ldg(reinterpret_cast<const int4*>(mp.mix[n] + c0)));
-                    H8 o;
+                    const int4 mq = LN_K == 1 ? coef[(2 + n) * LN_T + tid] : __ldg(reinterpret_cast<const int4*>(mp.mix[n] + c0));
+                    const __half2* m2 = reinterpret_cast<const __half2*>(&mq);
+                    int4 oq;
+                    __half2* o2 = reinterpret_cast<__half2*>(&oq);
 #pragma unroll
-                    for (int e = 0; e < 8; e++) o.f[e] = hr(cur.f[e] + hr(dx.f[e] * mv.f[e]));
-                    st8(mp.out[n] + m * C + c0, o);
+                    for (int e = 0; e < 4; e++) o2[e] = __hadd2_rn(c2[e], __hmul2_rn(dx[e], m2[e]));
+                    *reinterpret_cast<int4*>(mp.out[n] + m * C + c0) = oq;
                 }
                 prevq[j] = curq[j];
             }
     }
     if (t0 == 0) {   // new shift state = LN(x[b, T-1])
         if (t1 < T) {
-            load_row(x + ((size_t)b * T + T - 1) * C, xv);
-            normalise(xv, prevq);
+            load_row(x + ((size_t)b * T + T - 1) * C, v);
+            normalise(v, prevq);
         }
 #pragma unroll
         for (int j = 0; j < LN_K; j++)
-            if (j < nk) *reinterpret_cast<int4*>(srow + (j * LN_T + tid) * 8) = prevq[j];
+            if (FULL || j < nk) *reinterpret_cast<int4*>(srow + (j * LN_T + tid) * 8) = prevq[j];
     }
 }
 
@@ -417,51 +458,45 @@ int launch_embed_gather(int M, int C, int V, const int* tokens, const __half* em
     if (M <= 0) return 0;
     return launch_kernel(embed_gather_kernel, dim3(M), dim3(128), 0, s, pdl, 0, M, C, V, tokens, emb, x);
 }
-int launch_ln_shift_mix6(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
-                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl, const float* part,
-                         int n_part) {
-    if (B * T <= 0) return 0;
-    if (C > 4096) return -4;  // B200_ERR_UNSUPPORTED: one thread per 8 channels, 512 threads (every RWKV-7 g1 size has C <= 4096)
-    if (part && (T != 1 || n_part < 1)) return -1;
+template <int NMIX, bool FULL>
+int launch_ln_shift_mix_t(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift, long shift_stride,
+                          const int* slot_idx, const MixPtrs<NMIX>& mp, cudaStream_t s, bool pdl, const float* part, int n_part) {
     if (T == 1) {
-        const size_t coef_bytes = (size_t)(2 + 6) * 512 * 16;
+        const size_t coef_bytes = (size_t)(2 + NMIX) * 512 * 16;
         static bool attr_done[64] = {};
         int dev = 0;
         cudaGetDevice(&dev);
         if (dev < 0 || dev >= 64 || !attr_done[dev]) {
-            cudaError_t e = cudaFuncSetAttribute(ln_shift_mix_kernel<6, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)coef_bytes);
+            cudaError_t e = cudaFuncSetAttribute(ln_shift_mix_kernel<NMIX, 512, 1, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)coef_bytes);
             if (e != cudaSuccess) return (int)e;
             if (dev >= 0 && dev < 64) attr_done[dev] = true;
         }
-        return launch_kernel(ln_shift_mix_kernel<6, 512, 1>, dim3(B), dim3(512), coef_bytes, s, pdl, 0, T, C, 1, x, ln_w, ln_b, shift,
-                             shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+        return launch_kernel(ln_shift_mix_kernel<NMIX, 512, 1, FULL>, dim3(B), dim3(512), coef_bytes, s, pdl, 0, T, C, 1, x, ln_w, ln_b,
+                             shift, shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
     }
     const int strip = T >= 8 ? 8 : T;
-    return launch_kernel(ln_shift_mix_kernel<6, 128, 4>, dim3(B * ((T + strip - 1) / strip)), dim3(128), 0, s, pdl, 0, T, C, strip, x,
-                         ln_w, ln_b, shift, shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+    return launch_kernel(ln_shift_mix_kernel<NMIX, 128, 4, FULL>, dim3(B * ((T + strip - 1) / strip)), dim3(128), 0, s, pdl, 0, T, C,
+                         strip, x, ln_w, ln_b, shift, shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+}
+template <int NMIX>
+int launch_ln_shift_mix_n(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift, long shift_stride,
+                          const int* slot_idx, const MixPtrs<NMIX>& mp, cudaStream_t s, bool pdl, const float* part, int n_part) {
+    if (B * T <= 0) return 0;
+    if (C > 4096) return -4;  // B200_ERR_UNSUPPORTED: one thread per 8 channels, 512 threads (every RWKV-7 g1 size has C <= 4096)
+    if (part && (T != 1 || n_part < 1)) return -1;
+    return C == 4096 ? launch_ln_shift_mix_t<NMIX, true>(B, T, C, x, ln_w, ln_b, shift, shift_stride, slot_idx, mp, s, pdl, part, n_part)
+                     : launch_ln_shift_mix_t<NMIX, false>(B, T, C, x, ln_w, ln_b, shift, shift_stride, slot_idx, mp, s, pdl, part, n_part);
+}
+int launch_ln_shift_mix6(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
+                         long shift_stride, const int* slot_idx, const MixPtrs<6>& mp, cudaStream_t s, bool pdl, const float* part,
+                         int n_part) {
+    return launch_ln_shift_mix_n<6>(B, T, C, x, ln_w, ln_b, shift, shift_stride, slot_idx, mp, s, pdl, part, n_part);
 }
 int launch_ln_shift_mix1(int B, int T, int C, __half* x, const __half* ln_w, const __half* ln_b, __half* shift,
                          long shift_stride, const int* slot_idx, const MixPtrs<1>& mp, cudaStream_t s, bool pdl, const float* part,
                          int n_part) {
-    if (B * T <= 0) return 0;
-    if (C > 4096) return -4;
-    if (part && (T != 1 || n_part < 1)) return -1;
-    if (T == 1) {
-        const size_t coef_bytes = (size_t)(2 + 1) * 512 * 16;
-        static bool attr_done[64] = {};
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (dev < 0 || dev >= 64 || !attr_done[dev]) {
-            cudaError_t e = cudaFuncSetAttribute(ln_shift_mix_kernel<1, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)coef_bytes);
-            if (e != cudaSuccess) return (int)e;
-            if (dev >= 0 && dev < 64) attr_done[dev] = true;
-        }
-        return launch_kernel(ln_shift_mix_kernel<1, 512, 1>, dim3(B), dim3(512), coef_bytes, s, pdl, 0, T, C, 1, x, ln_w, ln_b, shift,
-                             shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
-    }
-    const int strip = T >= 8 ? 8 : T;
-    return launch_kernel(ln_shift_mix_kernel<1, 128, 4>, dim3(B * ((T + strip - 1) / strip)), dim3(128), 0, s, pdl, 0, T, C, strip, x,
-                         ln_w, ln_b, shift, shift_stride, slot_idx, mp, part, n_part, (long)B * T * C);
+    return launch_ln_shift_mix_n<1>(B, T, C, x, ln_w, ln_b, shift, shift_stride, slot_idx, mp, s, pdl, part, n_part);
 }
 int launch_ln_rows(int rows, int C, const __half* x, long row_step, long row_off, const __half* ln_w, const __half* ln_b,
                    __half* out, cudaStream_t s, bool pdl) {
