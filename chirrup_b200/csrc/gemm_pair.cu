@@ -10,7 +10,10 @@
 //
 //   warp 0 (one lane)   TMA producer: its CTA's A rows and W-half rows per 64-wide K block, completion on the LEADER's mbarrier
 //   warp 1 (one lane)   leader only: tcgen05.mma issuer; tcgen05.commit multicast frees the stage in both CTAs
-//   warps 2-5           epilogue: tcgen05.ld -> fp32 staging in shared memory -> coalesced bias / activation / residual -> fp16
+//   warps 2-9           epilogue: tcgen05.ld -> fp32 staging in shared memory -> coalesced bias / activation / residual -> fp16;
+//                       two warps per TMEM lane quarter (warp & 3), one takes the even 32-column units, the other the odd ones:
+//                       a one-tile launch's epilogue is on the step's critical path and a single warp per scheduler issues
+//                       one instruction per ~5 cycles (ncu: stall_wait / short_scoreboard), so a second warp halves it
 //
 // One launch carries up to PAIR_MAX_GROUP independent problems that share M (r,k,v and the four LoRA down-projections of a
 // layer are one launch), each with its own tile width BN (multiple of 32, <= 256).  K may additionally be split over the z
@@ -31,13 +34,15 @@
 namespace b200 {
 namespace {
 
-constexpr int PAIR_THREADS = 192;
+constexpr int PAIR_THREADS = 320;      // one-tile kernel: TMA warp, MMA warp, EIGHT epilogue warps (two per TMEM lane quarter)
+constexpr int PERSIST_THREADS = 192;   // persistent kernel: four epilogue warps (its epilogues hide under the next tile's MMAs)
 constexpr int PAIR_MAX_GROUP = 8;
 constexpr int PAIR_STAGE_BYTES = 32 * 1024;       // A half 128 x 64 fp16 (16 KiB) + W half up to 128 x 64 fp16 (16 KiB)
 constexpr int PAIR_MAX_STAGES = 6;
 constexpr int PAIR_MAX_SPLIT = 4;                 // cluster = 2 x 1 x S <= 8 CTAs (portable size)
 constexpr int PAIR_UNIT_FLOATS = 128 * 32;        // one parked unit: 128 rows x 32 columns fp32 = 16 KiB, thread-major
-constexpr int PAIR_STAGING_BYTES = 4 * 2 * 32 * STG_LD * 4;  // two 32 x 32(+4) fp32 buffers per epilogue warp = 36 KiB
+constexpr int PAIR_STAGING_BYTES = 4 * 2 * 32 * STG_LD * 4;  // two 32 x 32(+4) fp32 buffers per epilogue warp = 36 KiB (four warps: K-split reduce)
+constexpr int PAIR_STAGING_BYTES_8 = 2 * PAIR_STAGING_BYTES;  // the same for all eight epilogue warps (no K split / deferred split)
 constexpr uint32_t PAIR_TMEM_COLS = 256;
 
 struct PairProblem {
@@ -129,19 +134,21 @@ DEVI void tmem_ld_unit(uint32_t tmem_base, int q, int u, float (&v)[32]) {
 }
 
 // No K split: drain this warp's 32 accumulator rows unit by unit (the TMEM load of unit u+1 is in flight while unit u is emitted).
+// This warp takes units u0, u0 + 2, ... (u0 = 0 or 1: the two warps of a lane quarter).
 template <int EPI>
-DEVI void epilogue_direct(uint32_t tmem_base, int q, int lane, int n_valid, const EpiCtx& c, int row0, int n0, uint32_t stg0) {
+DEVI void epilogue_direct(uint32_t tmem_base, int q, int lane, int u0, int n_valid, const EpiCtx& c, int row0, int n0, uint32_t stg0) {
+    if (u0 >= n_valid) return;
     float va[32], vb[32];
-    tmem_ld_unit(tmem_base, q, 0, va);
+    tmem_ld_unit(tmem_base, q, u0, va);
 #pragma unroll 1
-    for (int u = 0; u < n_valid; u += 2) {
+    for (int u = u0; u < n_valid; u += 4) {
         tmem_ld_wait();
-        if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
+        if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, vb);
         emit_unit<EPI>(va, stg0, c, row0, n0 + u * 32, lane);
-        if (u + 1 < n_valid) {
+        if (u + 2 < n_valid) {
             tmem_ld_wait();
-            if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
-            emit_unit<EPI>(vb, stg0 + 32 * STG_LD * 4, c, row0, n0 + (u + 1) * 32, lane);
+            if (u + 4 < n_valid) tmem_ld_unit(tmem_base, q, u + 4, va);
+            emit_unit<EPI>(vb, stg0 + 32 * STG_LD * 4, c, row0, n0 + (u + 2) * 32, lane);
         }
     }
 }
@@ -345,28 +352,31 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
         __syncwarp();
     } else {
         pdl_wait();
-        const int q = warp & 3;  // TMEM lane quarter of this warp
+        const int q = warp & 3;          // TMEM lane quarter of this warp
+        const int u0 = (warp - 2) >> 2;  // its units: u0, u0 + 2, ...
         mbar_wait(accum_bar, 0);
         PPROBE(3);
         tc_fence_after();
         const int row = q * 32 + lane;  // this thread's accumulator row inside the CTA's 128
-        const uint32_t stg0 = smem_u32(smem) + (uint32_t)q * (2 * 32 * STG_LD * 4);
+        const uint32_t stg0 = smem_u32(smem) + (uint32_t)(warp - 2) * (2 * 32 * STG_LD * 4);
         if (S == 1) {
-            EPI_DISPATCH(epi, epilogue_direct<E>(tmem_base, q, lane, n_valid, ec, m0 + q * 32, n0, stg0));
+            EPI_DISPATCH(epi, epilogue_direct<E>(tmem_base, q, lane, u0, n_valid, ec, m0 + q * 32, n0, stg0));
+        } else if (u0 >= n_valid) {
+            // nothing for this warp (a tile of one unit)
         } else if (g.defer) {
             // deferred reduction: this split's raw fp32 partial, row-major, for the consumer kernel to sum (glue.h)
             float* dst = g.defer + (size_t)split * g.M * g.N;
             float va[32], vb[32];
-            tmem_ld_unit(tmem_base, q, 0, va);
+            tmem_ld_unit(tmem_base, q, u0, va);
 #pragma unroll 1
-            for (int u = 0; u < n_valid; u += 2) {
+            for (int u = u0; u < n_valid; u += 4) {
                 tmem_ld_wait();
-                if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
+                if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, vb);
                 emit_unit_f32(va, stg0, dst, g.N, g.M, g.N, m0 + q * 32, n0 + u * 32, lane);
-                if (u + 1 < n_valid) {
+                if (u + 2 < n_valid) {
                     tmem_ld_wait();
-                    if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
-                    emit_unit_f32(vb, stg0 + 32 * STG_LD * 4, dst, g.N, g.M, g.N, m0 + q * 32, n0 + (u + 1) * 32, lane);
+                    if (u + 4 < n_valid) tmem_ld_unit(tmem_base, q, u + 4, va);
+                    emit_unit_f32(vb, stg0 + 32 * STG_LD * 4, dst, g.N, g.M, g.N, m0 + q * 32, n0 + (u + 2) * 32, lane);
                 }
             }
         } else {
@@ -375,18 +385,18 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
             float4* my_part = reinterpret_cast<float4*>(
                 g.partials + ((((size_t)blockIdx.y * (gridDim.x >> 1) + tile) * 2 + pr) * S + split) * (size_t)8 * PAIR_UNIT_FLOATS) + row;
             float va[32], vb[32];
-            tmem_ld_unit(tmem_base, q, 0, va);
+            tmem_ld_unit(tmem_base, q, u0, va);
 #pragma unroll 1
-            for (int u = 0; u < n_valid; u += 2) {
+            for (int u = u0; u < n_valid; u += 4) {
                 tmem_ld_wait();
-                if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
+                if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, vb);
                 float4* dst = my_part + (size_t)u * (PAIR_UNIT_FLOATS / 4);
 #pragma unroll
                 for (int e = 0; e < 8; e++) __stcg(dst + e * 128, make_float4(va[4 * e], va[4 * e + 1], va[4 * e + 2], va[4 * e + 3]));
-                if (u + 1 < n_valid) {
+                if (u + 2 < n_valid) {
                     tmem_ld_wait();
-                    if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
-                    dst += PAIR_UNIT_FLOATS / 4;
+                    if (u + 4 < n_valid) tmem_ld_unit(tmem_base, q, u + 4, va);
+                    dst += 2 * (PAIR_UNIT_FLOATS / 4);
 #pragma unroll
                     for (int e = 0; e < 8; e++) __stcg(dst + e * 128, make_float4(vb[4 * e], vb[4 * e + 1], vb[4 * e + 2], vb[4 * e + 3]));
                 }
@@ -416,7 +426,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
                     bulk_load(land + (size_t)(j * S + z) * PAIR_UNIT_FLOATS, base + ((size_t)z * 8 + u) * PAIR_UNIT_FLOATS,
                               PAIR_UNIT_FLOATS * 4, red_bar);
         }
-        if (warp >= 2 && n_mine > 0) {
+        if (warp >= 2 && warp < 6 && n_mine > 0) {   // four warps: the landing zone takes the rest of the stage memory
             const int q = warp & 3;
             mbar_wait(red_bar, 0);
             EPI_DISPATCH(epi, epilogue_reduce<E>(smem_u32(land), S, split, n_valid, q * 32 + lane, lane, ec, m0 + q * 32, n0,
@@ -484,7 +494,7 @@ DEVI void mbar_arrive_cluster(uint32_t cluster_addr) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 
-__global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(const __grid_constant__ PairGroup grp, int gy) {
+__global__ void __launch_bounds__(PERSIST_THREADS, 1) pair_gemm_persist_kernel(const __grid_constant__ PairGroup grp, int gy) {
     extern __shared__ uint8_t smem_raw[];
     pdl_launch_dependents();
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -661,6 +671,7 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_persist_kernel(cons
 
 constexpr int PAIR_SMEM_BYTES = PAIR_MAX_STAGES * PAIR_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 static_assert(PAIR_STAGING_BYTES + 8 * PAIR_UNIT_FLOATS * 4 <= PAIR_MAX_STAGES * PAIR_STAGE_BYTES, "landing zone must fit the stages");
+static_assert(PAIR_STAGING_BYTES_8 <= PAIR_MAX_STAGES * PAIR_STAGE_BYTES, "eight staging pairs must fit the stages");
 
 // Pairs of CTAs (clusters of 2 x 1 x s) the device can hold at once.
 int pair_slots(int s) {
@@ -700,7 +711,7 @@ int persist_slots() {
     cudaFuncSetAttribute(pair_gemm_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PERSIST_SMEM_BYTES);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2, 1, 1);
-    cfg.blockDim = dim3(PAIR_THREADS);
+    cfg.blockDim = dim3(PERSIST_THREADS);
     cfg.dynamicSmemBytes = PERSIST_SMEM_BYTES;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -777,7 +788,7 @@ static int persist_group_launch(int n, const LinearDesc* d, int M, int gy, cudaS
     if (e != cudaSuccess) return (int)e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * pairs, 1, 1);
-    cfg.blockDim = dim3(PAIR_THREADS);
+    cfg.blockDim = dim3(PERSIST_THREADS);
     cfg.dynamicSmemBytes = PERSIST_SMEM_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
@@ -856,7 +867,7 @@ int ffn_chain_launch(int M, int C, int F, const void* kx, const void* Wk, void* 
     if (e != cudaSuccess) return (int)e;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * pairs, 1, 1);
-    cfg.blockDim = dim3(PAIR_THREADS);
+    cfg.blockDim = dim3(PERSIST_THREADS);
     cfg.dynamicSmemBytes = PERSIST_SMEM_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
