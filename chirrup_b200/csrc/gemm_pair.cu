@@ -35,7 +35,7 @@ namespace b200 {
 namespace {
 
 constexpr int PAIR_THREADS = 320;      // one-tile kernel: TMA warp, MMA warp, EIGHT epilogue warps (two per TMEM lane quarter)
-constexpr int PERSIST_THREADS = 192;   // persistent kernel: four epilogue warps (its epilogues hide under the next tile's MMAs)
+constexpr int PERSIST_THREADS = 320;   // persistent kernel: the same roles
 constexpr int PAIR_MAX_GROUP = 8;
 constexpr int PAIR_STAGE_BYTES = 32 * 1024;       // A half 128 x 64 fp16 (16 KiB) + W half up to 128 x 64 fp16 (16 KiB)
 constexpr int PAIR_MAX_STAGES = 6;
@@ -156,41 +156,28 @@ DEVI void epilogue_direct(uint32_t tmem_base, int q, int lane, int u0, int n_val
 // The same with ONE staging buffer per warp (the persistent kernel spends its shared memory on a sixth pipeline stage): a warp
 // barrier separates the reads of unit u from the writes of unit u+1.
 template <int EPI>
-DEVI void epilogue_direct_1buf(uint32_t tmem_base, int q, int lane, int n_valid, const EpiCtx& c, int row0, int n0, uint32_t stg0) {
-    float va[32], vb[32];
-    tmem_ld_unit(tmem_base, q, 0, va);
+DEVI void epilogue_direct_1buf(uint32_t tmem_base, int q, int lane, int u0, int n_valid, const EpiCtx& c, int row0, int n0,
+                               uint32_t stg0) {
 #pragma unroll 1
-    for (int u = 0; u < n_valid; u += 2) {
+    for (int u = u0; u < n_valid; u += 2) {
+        float va[32];
+        tmem_ld_unit(tmem_base, q, u, va);
         tmem_ld_wait();
-        if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
         __syncwarp();
         emit_unit<EPI>(va, stg0, c, row0, n0 + u * 32, lane);
-        if (u + 1 < n_valid) {
-            tmem_ld_wait();
-            if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
-            __syncwarp();
-            emit_unit<EPI>(vb, stg0, c, row0, n0 + (u + 1) * 32, lane);
-        }
     }
 }
 
 // Raw fp32 tile (deferred K-split partial, see GemmArgs::defer), one staging buffer per warp.
-DEVI void epilogue_f32_1buf(uint32_t tmem_base, int q, int lane, int n_valid, float* dst, int M, int N, int row0, int n0,
+DEVI void epilogue_f32_1buf(uint32_t tmem_base, int q, int lane, int u0, int n_valid, float* dst, int M, int N, int row0, int n0,
                             uint32_t stg0) {
-    float va[32], vb[32];
-    tmem_ld_unit(tmem_base, q, 0, va);
 #pragma unroll 1
-    for (int u = 0; u < n_valid; u += 2) {
+    for (int u = u0; u < n_valid; u += 2) {
+        float va[32];
+        tmem_ld_unit(tmem_base, q, u, va);
         tmem_ld_wait();
-        if (u + 1 < n_valid) tmem_ld_unit(tmem_base, q, u + 1, vb);
         __syncwarp();
         emit_unit_f32(va, stg0, dst, N, M, N, row0, n0 + u * 32, lane);
-        if (u + 1 < n_valid) {
-            tmem_ld_wait();
-            if (u + 2 < n_valid) tmem_ld_unit(tmem_base, q, u + 2, va);
-            __syncwarp();
-            emit_unit_f32(vb, stg0, dst, N, M, N, row0, n0 + (u + 1) * 32, lane);
-        }
     }
 }
 
@@ -450,8 +437,8 @@ __global__ void __launch_bounds__(PAIR_THREADS, 1) pair_gemm_kernel(const __grid
 // epilogue warps drain tile i while the MMA thread already accumulates tile i+1 and the TMA ring never drains between tiles.
 // Tile order: groups of PERSIST_GM consecutive M blocks, N-tile-major inside a group — the pairs of one wave share a few W
 // tiles and the group's activation rows stay in L2, so the weights stream from HBM once per group.
-constexpr int PERSIST_STAGES = 6;
-constexpr int PERSIST_STAGING_BYTES = 4 * 32 * STG_LD * 4;  // one 32 x 32(+4) fp32 buffer per epilogue warp = 18 KiB
+constexpr int PERSIST_STAGES = 5;
+constexpr int PERSIST_STAGING_BYTES = 8 * 32 * STG_LD * 4;  // one 32 x 32(+4) fp32 buffer per epilogue warp = 36 KiB
 constexpr int PERSIST_GM = 8;
 constexpr uint32_t PERSIST_TMEM_COLS = 512;
 constexpr int PERSIST_SMEM_BYTES = PERSIST_STAGES * PAIR_STAGE_BYTES + PERSIST_STAGING_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
@@ -502,7 +489,7 @@ __global__ void __launch_bounds__(PERSIST_THREADS, 1) pair_gemm_persist_kernel(c
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + PERSIST_STAGING_BYTES);
     uint64_t* empty_bar = full_bar + PERSIST_STAGES;
     uint64_t* tfull_bar = empty_bar + PERSIST_STAGES;   // [2] accumulator buffer complete (arrives in both CTAs)
-    uint64_t* tempty_bar = tfull_bar + 2;               // [2] accumulator buffer drained by all 8 epilogue warps of the pair (leader's)
+    uint64_t* tempty_bar = tfull_bar + 2;               // [2] accumulator buffer drained by all 16 epilogue warps of the pair (leader's)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
     const int warp = threadIdx.x >> 5;
@@ -524,7 +511,7 @@ __global__ void __launch_bounds__(PERSIST_THREADS, 1) pair_gemm_persist_kernel(c
         }
         for (int b = 0; b < 2; b++) {
             mbar_init(&tfull_bar[b], 1);
-            mbar_init(&tempty_bar[b], 8);
+            mbar_init(&tempty_bar[b], 16);
         }
         fence_barrier_init();
     }
@@ -629,7 +616,8 @@ __global__ void __launch_bounds__(PERSIST_THREADS, 1) pair_gemm_persist_kernel(c
     } else {
         pdl_wait();
         const int q = warp & 3;
-        const uint32_t stg0 = smem_u32(staging) + (uint32_t)q * (32 * STG_LD * 4);
+        const int u0 = (warp - 2) >> 2;
+        const uint32_t stg0 = smem_u32(staging) + (uint32_t)(warp - 2) * (32 * STG_LD * 4);
         const uint32_t tempty_leader0 = mapa_shared(smem_u32(&tempty_bar[0]), crank & ~1u);
         int j = 0;
         for (int tile = pair_id; tile < total; tile += n_pairs, j++) {
@@ -645,9 +633,9 @@ __global__ void __launch_bounds__(PERSIST_THREADS, 1) pair_gemm_persist_kernel(c
             tc_fence_after();
             const int epi = g.epi;
             if (g.defer) {
-                epilogue_f32_1buf(tmem_base + (uint32_t)buf * 256u, q, lane, n_valid, g.defer, g.M, g.N, c.m0 + pr * 128 + q * 32, c.n0, stg0);
+                epilogue_f32_1buf(tmem_base + (uint32_t)buf * 256u, q, lane, u0, n_valid, g.defer, g.M, g.N, c.m0 + pr * 128 + q * 32, c.n0, stg0);
             } else {
-                EPI_DISPATCH(epi, epilogue_direct_1buf<E>(tmem_base + (uint32_t)buf * 256u, q, lane, n_valid, ec, c.m0 + pr * 128 + q * 32, c.n0, stg0));
+                EPI_DISPATCH(epi, epilogue_direct_1buf<E>(tmem_base + (uint32_t)buf * 256u, q, lane, u0, n_valid, ec, c.m0 + pr * 128 + q * 32, c.n0, stg0));
             }
             tc_fence_before();
             __syncwarp();
@@ -850,7 +838,7 @@ int ffn_chain_launch(int M, int C, int F, const void* kx, const void* Wk, void* 
         P.bn = bn;
         P.kb0 = key ? 0 : (i - 1) * (F / S / BK);
         P.dep_flag = key ? -1 : i - 1;
-        P.dep_need = key ? 0 : (F / S / 256) * 8;   // every key tile of the split's hidden columns, 8 epilogue warps each
+        P.dep_need = key ? 0 : (F / S / 256) * 16;  // every key tile of the split's hidden columns, 16 epilogue warps each
         P.sig_flag = key ? 0 : -1;
         P.sig_div = key ? F / S / 256 : 1;
     }
