@@ -1,7 +1,7 @@
 #!/bin/bash
 # In-graph marginal cost of each kernel of the decode step: step time with that launch left out (B200_DEBUG_SKIP, model.cu).
 # Usage (GPU box): bash tools/knockout.sh > gpurun_out/knockout.txt
-run() { B200_DEBUG_SKIP=$1 timeout 300 python bench.py --steps 20 --warmup 5 --skip-cpu-baseline 2>/dev/null | tail -n 1 > /tmp/ko.json; python -c "
+run() { B200_DEBUG_SKIP=$1 timeout 300 python bench.py --steps 20 --warmup 5 --skip-cpu-baseline --no-engine 2>/dev/null | tail -n 1 > /tmp/ko.json; python -c "
 import json,sys
 d=json.load(open('/tmp/ko.json')); print('skip %4s %-28s ms_per_step %.3f  sm_mhz %s' % (sys.argv[1], sys.argv[2], d['ms_per_step'], d['clocks']['sm_mhz']))" $1 "$2"; }
 run 0 "(nothing)"

@@ -1,0 +1,17 @@
+set +e
+mkdir -p gpurun_out
+export CHIRRUP_B200_NO_BUILD=1
+timeout 1800 python -m pytest tests -m gpu -q > gpurun_out/r02_gpu_suite_final.log 2>&1
+echo "rc=$?" >> gpurun_out/r02_gpu_suite_final.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r02_smoke_final.log 2>&1
+echo "rc=$?" >> gpurun_out/r02_smoke_final.log
+timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/r02_bench_final.json 2> gpurun_out/r02_bench_final.err
+timeout 900 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/r02_bench_reference_final.json 2> gpurun_out/r02_bench_reference_final.err
+timeout 900 python bench.py --config prefill --steps 3 --warmup 1 --skip-cpu-baseline > gpurun_out/r02_bench_prefill_final.json 2> gpurun_out/r02_bench_prefill_final.err
+timeout 600 python bench.py --steps 2 --warmup 1 --no-engine --skip-cpu-baseline --no-graph > gpurun_out/b.log 2>&1 && \
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"(gemm|wkv7|ln_|embed|elapsed|tmix|argmax)" -c 3000 --csv --log-file gpurun_out/r02_decode_bench_launches.csv python bench.py --steps 2 --warmup 1 --no-engine --skip-cpu-baseline --no-graph > gpurun_out/ncu_a.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"(gemm|wkv7|ln_|embed|elapsed|tmix|argmax)" -c 517 --csv --log-file gpurun_out/r02_prefill_launches_final.csv python bench.py --config prefill --steps 1 --warmup 1 --skip-cpu-baseline > gpurun_out/ncu_p.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:wkv7_fused_one_kernel -s 40 -c 1 -f -o gpurun_out/r02_wkv_fused_one python bench.py --steps 2 --warmup 1 --no-engine --skip-cpu-baseline --no-graph > gpurun_out/ncu_b.log 2>&1
+timeout 900 ncu --set full --clock-control none -k regex:pair_gemm_kernel -s 30 -c 6 -f -o gpurun_out/r02_pair_gemm python bench.py --steps 2 --warmup 1 --no-engine --skip-cpu-baseline --no-graph > gpurun_out/ncu_c.log 2>&1
+timeout 900 ncu --set full --clock-control none -k regex:"(pair_gemm_persist_kernel|ln_shift_mix|wkv7_chunk)" -s 24 -c 8 -f -o gpurun_out/r02_prefill_kernels python bench.py --config prefill --steps 1 --warmup 1 --skip-cpu-baseline > gpurun_out/ncu_d.log 2>&1
+tail -n 3 gpurun_out/r02_gpu_suite_final.log gpurun_out/r02_smoke_final.log
