@@ -43,7 +43,7 @@ constexpr int TC = 16;        // tokens per chunk
 constexpr int NT = 128;       // threads per CTA
 constexpr int LDO = 72;       // halves per row of the 64-wide operand tiles (+8: conflict-free fragment loads)
 constexpr int LDS16 = 24;     // halves per row of the 16-wide operand tiles
-constexpr int LDY = 65;       // floats per row of the Y staging tile
+constexpr int LDY = 68;       // floats per row of the Y staging tile: 4 t + i -> the fragment store (t = 2tq, i = g) hits 32 banks
 
 DEVI float hr(float x) { return __half2float(__float2half_rn(x)); }
 
@@ -233,8 +233,9 @@ __global__ void __launch_bounds__(NT, 5) wkv7_chunk_kernel(const __grid_constant
                     ld[2 * u] = ld[2 * u + 1] = 0.f;
                 }
             }
-            *reinterpret_cast<float4*>(&sm.L[tk][cg * 8]) = make_float4(ld[0], ld[1], ld[2], ld[3]);
-            *reinterpret_cast<float4*>(&sm.L[tk][cg * 8 + 4]) = make_float4(ld[4], ld[5], ld[6], ld[7]);
+            // L row layout: position 32 j + 4 cg + e holds channel 8 cg + 4 j + e (a quarter-warp's 16-byte accesses are contiguous)
+            *reinterpret_cast<float4*>(&sm.L[tk][cg * 4]) = make_float4(ld[0], ld[1], ld[2], ld[3]);
+            *reinterpret_cast<float4*>(&sm.L[tk][32 + cg * 4]) = make_float4(ld[4], ld[5], ld[6], ld[7]);
             *reinterpret_cast<int4*>(&sm.v2s[tk][cg * 8]) = *reinterpret_cast<const int4*>(v2);
             *reinterpret_cast<int4*>(&sm.gs[tk][cg * 8]) = q_g;
             if (cg == 0) sm.bonus[tk] = hr(sbon);
@@ -249,15 +250,16 @@ __global__ void __launch_bounds__(NT, 5) wkv7_chunk_kernel(const __grid_constant
                 sm.L[s][tid] = c;
                 if (s == TC / 2 - 1) m = c;
             }
-            sm.em[tid] = ex2_approx_ftz(m);
-            sm.ecTm[tid] = ex2_approx_ftz(c - m);
+            const int chn = ((tid & 31) >> 2) * 8 + (tid >> 5) * 4 + (tid & 3);   // the channel at position tid of an L row
+            sm.em[chn] = ex2_approx_ftz(m);
+            sm.ecTm[chn] = ex2_approx_ftz(c - m);
         }
         __syncthreads();
         // ---- rescaled operands (|c - m| <= 8 * 0.875: plain ex2.approx, no range handling needed)
         {
-            const float4 c0 = *reinterpret_cast<const float4*>(&sm.L[tk][cg * 8]), c1 = *reinterpret_cast<const float4*>(&sm.L[tk][cg * 8 + 4]);
-            const float4 m0 = *reinterpret_cast<const float4*>(&sm.L[TC / 2 - 1][cg * 8]);
-            const float4 m1 = *reinterpret_cast<const float4*>(&sm.L[TC / 2 - 1][cg * 8 + 4]);
+            const float4 c0 = *reinterpret_cast<const float4*>(&sm.L[tk][cg * 4]), c1 = *reinterpret_cast<const float4*>(&sm.L[tk][32 + cg * 4]);
+            const float4 m0 = *reinterpret_cast<const float4*>(&sm.L[TC / 2 - 1][cg * 4]);
+            const float4 m1 = *reinterpret_cast<const float4*>(&sm.L[TC / 2 - 1][32 + cg * 4]);
             const float cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
             const float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
             __half2 at[4], rt[4], bt[4], kt[4];
@@ -408,8 +410,11 @@ __global__ void __launch_bounds__(NT, 5) wkv7_chunk_kernel(const __grid_constant
         {
             float y[8], s1 = 0.f, s2 = 0.f;
 #pragma unroll
+            const float4 y0 = *reinterpret_cast<const float4*>(&sm.ys[tk][cg * 8]), y1 = *reinterpret_cast<const float4*>(&sm.ys[tk][cg * 8 + 4]);
+            const float yr[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+#pragma unroll
             for (int e = 0; e < 8; e++) {
-                y[e] = hr(sm.ys[tk][cg * 8 + e]);   // the WKV output is an fp16 tensor in the reference
+                y[e] = hr(yr[e]);   // the WKV output is an fp16 tensor in the reference
                 s1 += y[e];
                 s2 = fmaf(y[e], y[e], s2);
             }
