@@ -30,6 +30,8 @@ SIGNATURES: Dict[str, tuple] = {
     "b200_spmv_forward": (_I, [_I, _I, _P, _P, _P, _P]),
     "b200_linear_f16": (_I, [_I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P, _I, _P, _L, _P]),
     "b200_linear_workspace_bytes": (_L, [_I, _I]),
+    "b200_linear_f16_static": (_I, [_I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P, _I, _P]),
+    "b200_linear_static_scratch_bytes": (_L, []),
     "b200_linear_group_f16": (_I, [_I, _P, _I, _P, _L, _P]),
     "b200_layer_norm_f16": (_I, [_I, _I, _P, _P, _P, _P, _P]),
     "b200_model_create": (_I, [_I, _I, _I, _I, _I, _I, _I, _P, _P, _P]),

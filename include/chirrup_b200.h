@@ -27,6 +27,7 @@ extern "C" {
 #define B200_ERR_NO_DRIVER (-2)   /* cuTensorMapEncodeTiled could not be resolved (no CUDA driver) */
 #define B200_ERR_WORKSPACE (-3)   /* workspace too small for this call */
 #define B200_ERR_UNSUPPORTED (-4)
+#define B200_ERR_TOO_LARGE (-5)   /* a size beyond the stated maximum of a fixed-scratch entry point (b200_linear_f16_static) */
 
 /* ABI version of this header (bumped on any signature change). */
 int b200_abi_version(void);
@@ -104,6 +105,27 @@ int b200_linear_f16(int M, int N, int K, const void* A, long lda, const void* W,
                     const void* bias, const void* residual, int epilogue, void* workspace, long workspace_bytes,
                     void* stream);
 long b200_linear_workspace_bytes(int max_M, int max_N);
+
+/*
+ * b200_linear_f16 for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO counterpart in the reference.
+ * Same arguments and results as b200_linear_f16 minus the workspace: the split-K scratch is a file-scope __device__ array of
+ * B200_LINEAR_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it until the process exits).
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *   limits   M <= B200_LINEAR_STATIC_MAX_M, N <= B200_LINEAR_STATIC_MAX_N, K <= B200_LINEAR_STATIC_MAX_K, else
+ *            B200_ERR_TOO_LARGE; a plan whose partials would not fit the scratch is not chosen, or the call returns
+ *            B200_ERR_WORKSPACE.
+ *   sharing  every call on a device uses the SAME array (it keeps the last call's contents; nothing in it has to start at zero:
+ *            each launch writes the partials it reads).  Calls that can overlap on the GPU — different streams, concurrent graph
+ *            replays — race on it: issue them on one stream.
+ */
+#define B200_LINEAR_STATIC_SCRATCH_BYTES (32 * 1024 * 1024)
+#define B200_LINEAR_STATIC_MAX_M 4096
+#define B200_LINEAR_STATIC_MAX_N 65536
+#define B200_LINEAR_STATIC_MAX_K 16384
+int b200_linear_f16_static(int M, int N, int K, const void* A, long lda, const void* W, long ldw, void* out, long ldo,
+                           const void* bias, const void* residual, int epilogue, void* stream);
+long b200_linear_static_scratch_bytes(void);
 
 /*
  * Up to 8 independent linear layers that share M in ONE launch (e.g. the r, k, v projections and the four LoRA
